@@ -1,0 +1,218 @@
+/*
+ * nanodiloco_b200.h -- C ABI of libnanodiloco_b200.so
+ *
+ * Hand-written sm_100a CUDA kernels for the one hot path of SJCaldwell/NanoDiloco:
+ * the DiLoCo outer synchronisation (pseudo-gradient -> cross-worker average ->
+ * Nesterov outer SGD -> copy-back) and the inner clip + AdamW step.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; no torch / C++ types cross this boundary.
+ *   - every pointer is DEVICE memory owned by the caller unless the name says
+ *     `host`; the library never allocates or frees caller-visible memory.
+ *   - all work is enqueued on the caller's stream (`nd_stream_t` is a
+ *     `cudaStream_t`); no call synchronises the device unless documented.
+ *   - every function returns 0 on success, a non-zero ND_E* code otherwise;
+ *     `nd_last_error()` then holds a human-readable message (thread-local).
+ *   - `n` counts ELEMENTS.  Buffers may have any alignment; the 128-bit
+ *     vectorised path is taken when every pointer of a call is 16-byte aligned
+ *     (always true for the flat buffers nanodiloco_b200.Diloco builds).
+ *
+ * Citations `diloco.py:NN`, `main.py:NN` are into the reference repository
+ * (nanodiloco/diloco/diloco.py, nanodiloco/main.py); `torch:` into the torch
+ * sources the reference calls.
+ */
+#ifndef NANODILOCO_B200_H
+#define NANODILOCO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct CUstream_st* nd_stream_t; /* == cudaStream_t */
+
+/* element types of the workers' local ("working") parameter copy */
+enum { ND_F32 = 0, ND_BF16 = 1 };
+
+/* error codes (negative: library; the message carries the CUDA/NCCL string) */
+enum {
+    ND_OK = 0,
+    ND_EINVAL = 1,   /* bad argument (null pointer, n < 0, unknown dtype, W out of range) */
+    ND_ECUDA = 2,    /* a CUDA runtime call or kernel launch failed */
+    ND_ENCCL = 3,    /* an NCCL call failed or libnccl could not be loaded */
+    ND_ESTATE = 4    /* call made in the wrong state (e.g. context not initialised) */
+};
+
+#define ND_MAX_WORKERS 16 /* most worker copies one fused launch can read */
+
+/* One row of a multi-tensor table (lives in DEVICE memory, built once by the
+ * caller because parameter storage never moves -- unlike diloco.py:50, which
+ * rebinds .data each outer step).  `ptr[k]` meaning depends on the call. */
+typedef struct {
+    void* ptr[4];
+    int64_t numel;
+    int64_t first_chunk; /* index of this tensor's first ND_CHUNK-sized chunk in the launch */
+} nd_tensor_desc;
+
+#define ND_CHUNK 16384 /* elements per multi-tensor chunk */
+
+/* ---- library ---------------------------------------------------------- */
+
+int nd_version(void);
+const char* nd_last_error(void);
+
+/* Bytes of zero-initialised device scratch the norm-producing calls need
+ * (per-block partial sums + a self-resetting arrival counter).  Zero it once
+ * after allocation; calls leave it ready for the next call.  Calls that share
+ * one scratch buffer must be ordered on the GPU (same stream or events). */
+size_t nd_scratch_bytes(void);
+
+/* ---- (1) pseudo-gradient ---------------------------------------------- */
+
+/* pg[i] = master[i] - (float)local[i]
+ * Replaces diloco.py:47-48 (`last_sync.to(device)`; `last_sync - replica.data`)
+ * -- the master copy is already in HBM, so the per-tensor H2D copy is gone. */
+int nd_pseudo_grad(const float* master, const void* local, int local_dtype,
+                   float* pg, int64_t n, nd_stream_t stream);
+
+/* Multi-tensor form over a device table: ptr[0]=master, ptr[1]=local, ptr[2]=pg.
+ * Replaces the per-tensor Python loop diloco.py:46-48 with one launch. */
+int nd_pseudo_grad_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+                      int local_dtype, nd_stream_t stream);
+
+/* ---- (2) fused outer update ------------------------------------------- */
+
+/* Outer Nesterov-SGD on one shard after the cross-worker SUM:
+ *   g = pg_sum / world                         (the AVG of diloco.py:49)
+ *   g = g + wd*p        if wd != 0             torch:optim/sgd.py:345-356
+ *   b = g               if first_step          torch:optim/sgd.py:361-363
+ *   b = b*mu ; b = b + (1-dampening)*g  else   torch:optim/sgd.py:365
+ *   d = g + mu*b        if nesterov else b     torch:optim/sgd.py:367-370
+ *   p = p + (-lr)*d                            torch:optim/sgd.py:380
+ * master <- p, mom <- b, local_out <- p (cast to local_dtype): the rewind of
+ * diloco.py:50, the step of diloco.py:52 and the snapshot of diloco.py:54 in a
+ * single HBM pass.  Rounding follows torch exactly (each `alpha=` form is one
+ * FMA, `b*mu` is its own rounding), so W<=2 results are bit-identical.
+ * local_out may be NULL (shard-only update; the all-gather writes the copy).
+ * sumsq_out (nullable): receives sum(g*g) over the n elements (the averaged
+ * pseudo-gradient's squared norm); needs `scratch` (nd_scratch_bytes()). */
+int nd_outer_nesterov(float* master, float* mom, const float* pg_sum,
+                      void* local_out, int local_dtype, int64_t n,
+                      float world, float lr, float mu, float dampening, float wd,
+                      int nesterov, int first_step,
+                      float* sumsq_out, void* scratch, nd_stream_t stream);
+
+/* Kernels (1)+(2) in one pass for W worker copies addressable from this GPU
+ * (W=1: the single-GPU outer step; W>1: peer-mapped copies over NVLink, or
+ * several workers emulated on one GPU):
+ *   g = ( sum_{w=0..W-1} (master - local_w) ) / W     diloco.py:48-49, summed in worker order
+ *   ...update as nd_outer_nesterov...
+ *   master <- p, mom <- b, local_w <- p for every w    diloco.py:50-54
+ * `locals_host` is a HOST array of W device pointers (copied into the launch
+ * arguments).  24 B/element of HBM traffic at W=1; the pseudo-gradient never
+ * touches memory. */
+int nd_outer_fused(float* master, float* mom, void* const* locals_host, int W,
+                   int local_dtype, int64_t n,
+                   float lr, float mu, float dampening, float wd,
+                   int nesterov, int first_step,
+                   float* sumsq_out, void* scratch, nd_stream_t stream);
+
+/* Multi-tensor form of nd_outer_fused for W=1:
+ * ptr[0]=master, ptr[1]=mom, ptr[2]=local.  Replaces diloco.py:46-54. */
+int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+                      int local_dtype, float lr, float mu, float dampening, float wd,
+                      int nesterov, int first_step, nd_stream_t stream);
+
+/* ---- (3) inner step: clip_grad_norm_ + AdamW --------------------------- */
+
+/* out[0] = sum(g[i]^2), deterministic (fixed reduction tree, fp32 partials
+ * combined in double).  First half of torch.nn.utils.clip_grad_norm_
+ * (diloco.py:57; torch:nn/utils/clip_grad.py:93-108).  Needs `scratch`. */
+int nd_sumsq(const void* g, int dtype, int64_t n, float* out, void* scratch,
+             nd_stream_t stream);
+
+/* Multi-tensor form: ptr[0]=grad. */
+int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+                float* out, void* scratch, nd_stream_t stream);
+
+/* Fused clip + AdamW (diloco.py:57-58; torch:nn/utils/clip_grad.py:165-174,
+ * torch:optim/adam.py:692-800 with decoupled weight decay):
+ *   coef = min(1, max_norm / (sqrt(*sumsq_dev) + 1e-6))   (1 if sumsq_dev is NULL)
+ *   g  = g*coef
+ *   p  = p*(1 - lr*wd)
+ *   m  = m + (1-beta1)*(g - m)
+ *   v  = v*beta2 ; v = v + (1-beta2)*(g*g)
+ *   p  = p + (-lr/bc1) * ( m / (sqrt(v)/sqrt(bc2) + eps) )
+ * with bc1 = 1-beta1^step, bc2 = 1-beta2^step formed in double on the host like
+ * torch does, `step` 1-based.  Rounding follows torch's CUDA foreach kernels
+ * (torch:include/ATen/native/cuda/DeviceAddCmulCdiv.cuh:10-32).  The clip
+ * coefficient is read on the device: no host synchronisation anywhere.
+ * zero_grad != 0 also writes g <- 0 (the zero_grad of diloco.py:60, fused). */
+int nd_adamw(float* p, float* g, float* m, float* v, int64_t n,
+             double lr, double beta1, double beta2, double eps, double weight_decay,
+             int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
+             nd_stream_t stream);
+
+/* Multi-tensor form: ptr[0]=p, ptr[1]=g, ptr[2]=m, ptr[3]=v. */
+int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+                double lr, double beta1, double beta2, double eps, double weight_decay,
+                int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
+                nd_stream_t stream);
+
+/* ---- sharded multi-GPU outer sync (one process per GPU) ----------------- */
+
+/* 128-byte NCCL unique id, produced on rank 0 and handed to every rank by the
+ * host (torch.distributed broadcast / store). */
+#define ND_UNIQUE_ID_BYTES 128
+int nd_nccl_unique_id(char out_host[ND_UNIQUE_ID_BYTES]);
+
+typedef struct nd_sync_ctx nd_sync_ctx;
+
+/* Creates this rank's context: an NCCL communicator over `world` ranks (the
+ * replacement of utils.py:41-43's process group for this path), `n_streams`
+ * side streams and the events that join them to the caller's stream.  Must be
+ * called by all ranks together, with the calling thread's current CUDA device
+ * set.  bucket_elems: elements per pipeline bucket (rounded up to a multiple of
+ * 4*world). */
+int nd_sync_ctx_create(const char unique_id_host[ND_UNIQUE_ID_BYTES], int world, int rank,
+                       int64_t bucket_elems, int n_streams, nd_sync_ctx** out);
+int nd_sync_ctx_destroy(nd_sync_ctx* ctx);
+
+/* Elements of the padded flat parameter space for n real elements (multiple of
+ * bucket size boundaries so that every bucket splits into `world` equal,
+ * 16-byte-aligned shards), and the number of elements of sharded state
+ * (master shard / momentum shard) this rank must hold. */
+int64_t nd_sync_padded_elems(const nd_sync_ctx* ctx, int64_t n);
+int64_t nd_sync_shard_elems(const nd_sync_ctx* ctx, int64_t n);
+/* Elements per pipeline bucket after rounding.  Bucket b covers padded elements
+ * [b*B, min((b+1)*B, n_padded)); rank r owns the r-th of its `world` equal
+ * slices, and the rank's shard is the concatenation of its slices in bucket order. */
+int64_t nd_sync_bucket_elems(const nd_sync_ctx* ctx);
+
+/* The whole outer step of diloco.py:34-54 across `world` GPUs.  Per bucket b,
+ * pipelined over the side streams:
+ *   K1   pg_b = master_b - local_b                       (all ranks, full bucket)
+ *   RS   ncclReduceScatter(pg_b, sum) -> this rank's 1/world slice
+ *   K2   nd_outer_nesterov on the slice (master shard, momentum shard), writing
+ *        the new parameters into this rank's slice of local_b
+ *   AG   ncclAllGather(local_b) in place; master_b <- local_b rides with it
+ * local:      padded flat working parameters (fp32), n_padded elements
+ * master:     padded flat last-sync copy (fp32), n_padded elements (replicated)
+ * mom_shard:  this rank's momentum slices, nd_sync_shard_elems() elements
+ * pg:         staging for the pseudo-gradient, n_padded elements
+ * On return the work is ordered on `stream`; nothing is synchronised. */
+int nd_outer_sync(nd_sync_ctx* ctx, float* local, float* master, float* mom_shard, float* pg,
+                  int64_t n_padded, float lr, float mu, float dampening, float wd,
+                  int nesterov, int first_step, nd_stream_t stream);
+
+/* Device milliseconds of the last nd_outer_sync on this rank (blocks until it
+ * has finished) -- what the reference's dead `avg_sync_time` (diloco.py:62-64)
+ * promised. */
+int nd_sync_last_ms(nd_sync_ctx* ctx, float* ms_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NANODILOCO_B200_H */

@@ -1,0 +1,629 @@
+// nd_kernels.cu -- sm_100a kernels of the DiLoCo outer-sync hot path + their C ABI.
+//
+// Kernel inventory (each is one HBM pass; algorithmic bytes/element in brackets):
+//   pseudo_grad        pg = master - local                         [12 fp32 | 10 bf16 local]
+//   outer_shard        AVG-scale + Nesterov + master/mom update + copy-back on a shard
+//                                                                  [24 fp32 | 22 bf16]
+//   outer_fused<W>     both of the above for W addressable worker copies, pseudo-gradient
+//                      kept in registers                           [16 + 8W fp32]
+//   sumsq              sum of squares (clip_grad_norm_ stage 1)     [4]
+//   adamw              clip-scale + AdamW (+ optional zero_grad)    [28 (+4)]
+// and table-driven multi-tensor forms of each for non-flat callers.
+//
+// Structure: an "Op" describes how to load / compute / store one group of four
+// consecutive elements (or one element on the scalar path).  Two drivers run an
+// Op: `flat_kernel` over one contiguous range and `table_kernel` over a device
+// table of tensors cut into ND_CHUNK-element chunks.  Both issue all loads of
+// kUnroll independent groups before any dependent arithmetic or store, so each
+// thread keeps kUnroll x (#inputs) 128-bit requests in flight.
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+
+#include "nd_common.cuh"
+#include "nd_error.h"
+
+namespace nd {
+
+// ===========================================================================
+// Ops
+// ===========================================================================
+
+template <bool BF16>
+struct PseudoGradOp {
+    static constexpr bool kHasSum = false;
+    const float* master;
+    const void* local;
+    float* pg;
+    struct Regs { float4 a, b; };
+
+    __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
+        master = static_cast<const float*>(d.ptr[0]) + off;
+        local = static_cast<const typename Local<BF16>::T*>(d.ptr[1]) + off;
+        pg = static_cast<float*>(d.ptr[2]) + off;
+    }
+    __device__ __forceinline__ bool aligned() const {
+        return ((reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(pg)) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(local) & (BF16 ? 7 : 15)) == 0;
+    }
+    __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
+        r.a = ld_stream(master + i);
+        r.b = Local<BF16>::ld4(local, i);
+    }
+    __device__ __forceinline__ void compute4(Regs& r) {
+        r.a.x = __fsub_rn(r.a.x, r.b.x); r.a.y = __fsub_rn(r.a.y, r.b.y);
+        r.a.z = __fsub_rn(r.a.z, r.b.z); r.a.w = __fsub_rn(r.a.w, r.b.w);
+    }
+    __device__ __forceinline__ void store4(int64_t i, const Regs& r) const { st_stream(pg + i, r.a); }
+    __device__ __forceinline__ void scalar(int64_t i) {
+        pg[i] = __fsub_rn(master[i], Local<BF16>::ld1(local, i));
+    }
+};
+
+// Outer update of a shard whose pseudo-gradient SUM is already in memory.
+template <bool BF16, bool SUM>
+struct OuterShardOp {
+    static constexpr bool kHasSum = SUM;
+    float* master;
+    float* mom;
+    const float* pg_sum;
+    void* local_out;  // nullable
+    float world;
+    OuterHyper h;
+    float acc;
+    struct Regs { float4 p, b, g; };
+
+    __device__ __forceinline__ void rebase(const nd_tensor_desc&, int64_t) {}
+    __device__ __forceinline__ bool aligned() const {
+        return ((reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(mom) |
+                 reinterpret_cast<uintptr_t>(pg_sum)) & 15) == 0 &&
+               (reinterpret_cast<uintptr_t>(local_out) & (BF16 ? 7 : 15)) == 0;
+    }
+    __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
+        r.p = ld_stream(master + i);
+        r.g = ld_stream(pg_sum + i);
+        r.b = h.first_step ? make_float4(0.f, 0.f, 0.f, 0.f) : ld_stream(mom + i);
+    }
+    __device__ __forceinline__ void one(float& p, float& b, float s) {
+        float g = __fdiv_rn(s, world);
+        if (SUM) acc = __fmaf_rn(g, g, acc);
+        outer_update(g, p, b, h);
+    }
+    __device__ __forceinline__ void compute4(Regs& r) {
+        one(r.p.x, r.b.x, r.g.x); one(r.p.y, r.b.y, r.g.y);
+        one(r.p.z, r.b.z, r.g.z); one(r.p.w, r.b.w, r.g.w);
+    }
+    __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
+        st_stream(master + i, r.p);
+        st_stream(mom + i, r.b);
+        if (local_out) Local<BF16>::st4(local_out, i, r.p);
+    }
+    __device__ __forceinline__ void scalar(int64_t i) {
+        float p = master[i], b = h.first_step ? 0.0f : mom[i];
+        one(p, b, pg_sum[i]);
+        master[i] = p; mom[i] = b;
+        if (local_out) Local<BF16>::st1(local_out, i, p);
+    }
+};
+
+struct LocalPtrs { void* p[ND_MAX_WORKERS]; };
+
+// Kernels (1)+(2) fused over W worker copies.  W > 0: compile-time count, all W
+// local loads issued up front; W == 0: run-time count (9..ND_MAX_WORKERS).
+template <int W, bool BF16, bool SUM>
+struct OuterFusedOp {
+    static constexpr bool kHasSum = SUM;
+    static constexpr int kW = W > 0 ? W : 1;
+    float* master;
+    float* mom;
+    LocalPtrs locals;
+    int w_rt;  // run-time W
+    float world;
+    OuterHyper h;
+    float acc;
+    struct Regs { float4 p, b; float4 l[kW]; };
+
+    __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
+        master = static_cast<float*>(d.ptr[0]) + off;
+        mom = static_cast<float*>(d.ptr[1]) + off;
+        locals.p[0] = static_cast<typename Local<BF16>::T*>(d.ptr[2]) + off;
+    }
+    __device__ __forceinline__ bool aligned() const {
+        uintptr_t a = reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(mom);
+        uintptr_t l = 0;
+        const int w = W > 0 ? W : w_rt;
+        for (int k = 0; k < w; ++k) l |= reinterpret_cast<uintptr_t>(locals.p[k]);
+        return (a & 15) == 0 && (l & (BF16 ? 7 : 15)) == 0;
+    }
+    __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
+        r.p = ld_stream(master + i);
+        r.b = h.first_step ? make_float4(0.f, 0.f, 0.f, 0.f) : ld_stream(mom + i);
+        if (W > 0) {
+#pragma unroll
+            for (int k = 0; k < kW; ++k) r.l[k] = Local<BF16>::ld4(locals.p[k], i);
+        } else {
+            // run-time W: accumulate as we go (sum of (master - local_w) in worker order)
+            float4 s;
+            for (int k = 0; k < w_rt; ++k) {
+                float4 l = Local<BF16>::ld4(locals.p[k], i);
+                float4 d = make_float4(__fsub_rn(r.p.x, l.x), __fsub_rn(r.p.y, l.y),
+                                       __fsub_rn(r.p.z, l.z), __fsub_rn(r.p.w, l.w));
+                if (k == 0) s = d;
+                else s = make_float4(__fadd_rn(s.x, d.x), __fadd_rn(s.y, d.y),
+                                     __fadd_rn(s.z, d.z), __fadd_rn(s.w, d.w));
+            }
+            r.l[0] = s;
+        }
+    }
+    __device__ __forceinline__ void one(float& p, float& b, float s) {
+        float g = (W == 1) ? s : __fdiv_rn(s, world);
+        if (SUM) acc = __fmaf_rn(g, g, acc);
+        outer_update(g, p, b, h);
+    }
+    __device__ __forceinline__ void compute4(Regs& r) {
+        float4 s;
+        if (W > 0) {
+            s = make_float4(__fsub_rn(r.p.x, r.l[0].x), __fsub_rn(r.p.y, r.l[0].y),
+                            __fsub_rn(r.p.z, r.l[0].z), __fsub_rn(r.p.w, r.l[0].w));
+#pragma unroll
+            for (int k = 1; k < kW; ++k) {
+                s.x = __fadd_rn(s.x, __fsub_rn(r.p.x, r.l[k].x));
+                s.y = __fadd_rn(s.y, __fsub_rn(r.p.y, r.l[k].y));
+                s.z = __fadd_rn(s.z, __fsub_rn(r.p.z, r.l[k].z));
+                s.w = __fadd_rn(s.w, __fsub_rn(r.p.w, r.l[k].w));
+            }
+        } else {
+            s = r.l[0];
+        }
+        one(r.p.x, r.b.x, s.x); one(r.p.y, r.b.y, s.y);
+        one(r.p.z, r.b.z, s.z); one(r.p.w, r.b.w, s.w);
+    }
+    __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
+        st_stream(master + i, r.p);
+        st_stream(mom + i, r.b);
+        const int w = W > 0 ? W : w_rt;
+#pragma unroll
+        for (int k = 0; k < w; ++k) Local<BF16>::st4(locals.p[k], i, r.p);
+    }
+    __device__ __forceinline__ void scalar(int64_t i) {
+        const int w = W > 0 ? W : w_rt;
+        float p = master[i], b = h.first_step ? 0.0f : mom[i];
+        float s = __fsub_rn(p, Local<BF16>::ld1(locals.p[0], i));
+        for (int k = 1; k < w; ++k) s = __fadd_rn(s, __fsub_rn(p, Local<BF16>::ld1(locals.p[k], i)));
+        float g = (w == 1) ? s : __fdiv_rn(s, world);
+        if (SUM) acc = __fmaf_rn(g, g, acc);
+        outer_update(g, p, b, h);
+        master[i] = p; mom[i] = b;
+        for (int k = 0; k < w; ++k) Local<BF16>::st1(locals.p[k], i, p);
+    }
+};
+
+template <bool BF16>
+struct SumsqOp {
+    static constexpr bool kHasSum = true;
+    const void* g;
+    float acc;
+    struct Regs { float4 a; };
+    __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
+        g = static_cast<const typename Local<BF16>::T*>(d.ptr[0]) + off;
+    }
+    __device__ __forceinline__ bool aligned() const {
+        return (reinterpret_cast<uintptr_t>(g) & (BF16 ? 7 : 15)) == 0;
+    }
+    __device__ __forceinline__ void load4(int64_t i, Regs& r) const { r.a = Local<BF16>::ld4(g, i); }
+    __device__ __forceinline__ void compute4(Regs& r) {
+        acc = __fmaf_rn(r.a.x, r.a.x, acc); acc = __fmaf_rn(r.a.y, r.a.y, acc);
+        acc = __fmaf_rn(r.a.z, r.a.z, acc); acc = __fmaf_rn(r.a.w, r.a.w, acc);
+    }
+    __device__ __forceinline__ void store4(int64_t, const Regs&) const {}
+    __device__ __forceinline__ void scalar(int64_t i) {
+        float x = Local<BF16>::ld1(g, i);
+        acc = __fmaf_rn(x, x, acc);
+    }
+};
+
+struct AdamHyper {
+    float decay;      // 1 - lr*wd              (adam.py:692)
+    float w1;         // 1 - beta1              (adam.py:705-707)
+    float b2;         // beta2                  (adam.py:709)
+    float w2;         // 1 - beta2              (adam.py:722-724)
+    float step_size;  // -lr / bc1              (adam.py:779)
+    float bc2_sqrt;   // sqrt(1 - beta2^step)   (adam.py:781)
+    float eps;
+    float max_norm;
+    int has_decay, zero_grad;
+};
+
+struct AdamWOp {
+    static constexpr bool kHasSum = false;
+    float* p; float* g; float* m; float* v;
+    const float* sumsq;  // nullable
+    AdamHyper h;
+    float coef;
+    struct Regs { float4 p, g, m, v; };
+
+    __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
+        p = static_cast<float*>(d.ptr[0]) + off; g = static_cast<float*>(d.ptr[1]) + off;
+        m = static_cast<float*>(d.ptr[2]) + off; v = static_cast<float*>(d.ptr[3]) + off;
+    }
+    // clip_grad.py:165-168, evaluated on the device so the host never waits for the norm
+    __device__ __forceinline__ void prologue() {
+        coef = 1.0f;
+        if (sumsq) {
+            float total = sqrtf(__ldg(sumsq));
+            coef = fminf(__fdiv_rn(h.max_norm, total + 1e-6f), 1.0f);
+        }
+    }
+    __device__ __forceinline__ bool aligned() const {
+        return ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
+                 reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+    }
+    __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
+        r.p = ld_stream(p + i); r.g = ld_stream(g + i);
+        r.m = ld_stream(m + i); r.v = ld_stream(v + i);
+    }
+    __device__ __forceinline__ void one(float& pi, float gi, float& mi, float& vi) const {
+        gi = __fmul_rn(gi, coef);
+        if (h.has_decay) pi = __fmul_rn(pi, h.decay);
+        mi = __fmaf_rn(h.w1, __fsub_rn(gi, mi), mi);
+        vi = __fmul_rn(vi, h.b2);
+        vi = __fmaf_rn(h.w2, __fmul_rn(gi, gi), vi);
+        float den = __fadd_rn(__fdiv_rn(__fsqrt_rn(vi), h.bc2_sqrt), h.eps);
+        pi = __fmaf_rn(h.step_size, __fdiv_rn(mi, den), pi);
+    }
+    __device__ __forceinline__ void compute4(Regs& r) const {
+        one(r.p.x, r.g.x, r.m.x, r.v.x); one(r.p.y, r.g.y, r.m.y, r.v.y);
+        one(r.p.z, r.g.z, r.m.z, r.v.z); one(r.p.w, r.g.w, r.m.w, r.v.w);
+    }
+    __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
+        st_stream(p + i, r.p); st_stream(m + i, r.m); st_stream(v + i, r.v);
+        if (h.zero_grad) st_stream(g + i, make_float4(0.f, 0.f, 0.f, 0.f));
+    }
+    __device__ __forceinline__ void scalar(int64_t i) const {
+        float pi = p[i], mi = m[i], vi = v[i];
+        one(pi, g[i], mi, vi);
+        p[i] = pi; m[i] = mi; v[i] = vi;
+        if (h.zero_grad) g[i] = 0.0f;
+    }
+};
+
+template <class Op, class = void>
+struct HasPrologue { static constexpr bool value = false; };
+template <class Op>
+struct HasPrologue<Op, decltype(std::declval<Op&>().prologue(), void())> {
+    static constexpr bool value = true;
+};
+
+// ===========================================================================
+// Drivers
+// ===========================================================================
+
+// Runs `op` over elements [0, count) of its (already rebased) pointers using
+// `nthreads` cooperating threads of which this one is `tid`.
+template <int U, class Op>
+__device__ __forceinline__ void run_range(Op& op, int64_t count, int64_t tid, int64_t nthreads) {
+    if (op.aligned()) {
+        const int64_t nvec = count >> 2;
+        int64_t i = tid;
+        // main loop: U independent groups per thread, all loads first
+        for (; i + (U - 1) * nthreads < nvec; i += U * nthreads) {
+            typename Op::Regs r[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) op.load4((i + u * nthreads) << 2, r[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) op.compute4(r[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) op.store4((i + u * nthreads) << 2, r[u]);
+        }
+        for (; i < nvec; i += nthreads) {
+            typename Op::Regs r;
+            op.load4(i << 2, r);
+            op.compute4(r);
+            op.store4(i << 2, r);
+        }
+        // ragged tail: the last count % 4 elements
+        const int64_t t = (nvec << 2) + tid;
+        if (t < count) op.scalar(t);
+    } else {
+        for (int64_t i = tid; i < count; i += nthreads) op.scalar(i);
+    }
+}
+
+template <int U, int MINB, class Op>
+__global__ void __launch_bounds__(kThreads, MINB) flat_kernel(Op op, int64_t n, Scratch* sc, float* sum_out) {
+    if constexpr (HasPrologue<Op>::value) op.prologue();
+    if constexpr (Op::kHasSum) op.acc = 0.0f;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    run_range<U>(op, n, tid, nthreads);
+    if constexpr (Op::kHasSum) grid_sum_to(op.acc, sc, sum_out);
+}
+
+// One CTA per chunk (grid-stride).  The table is small (hundreds of rows) and
+// L2/L1-resident; a binary search per chunk is noise next to 16K elements of
+// HBM traffic.
+template <int U, int MINB, class Op>
+__global__ void __launch_bounds__(kThreads, MINB) table_kernel(Op op, const nd_tensor_desc* __restrict__ tab, int T,
+                                                               int64_t total_chunks, Scratch* sc, float* sum_out) {
+    if constexpr (HasPrologue<Op>::value) op.prologue();
+    if constexpr (Op::kHasSum) op.acc = 0.0f;
+    for (int64_t c = blockIdx.x; c < total_chunks; c += gridDim.x) {
+        int lo = 0, hi = T - 1;
+        while (lo < hi) {  // last row with first_chunk <= c
+            int mid = (lo + hi + 1) >> 1;
+            if (__ldg(&tab[mid].first_chunk) <= c) lo = mid; else hi = mid - 1;
+        }
+        nd_tensor_desc d = tab[lo];
+        const int64_t off = (c - d.first_chunk) * (int64_t)ND_CHUNK;
+        int64_t count = d.numel - off;
+        if (count > ND_CHUNK) count = ND_CHUNK;
+        if (count <= 0) continue;
+        Op local_op = op;
+        local_op.rebase(d, off);
+        run_range<U>(local_op, count, threadIdx.x, blockDim.x);
+        if constexpr (Op::kHasSum) op.acc = local_op.acc;
+    }
+    if constexpr (Op::kHasSum) grid_sum_to(op.acc, sc, sum_out);
+}
+
+// ===========================================================================
+// Host side
+// ===========================================================================
+
+static int g_sm_count[64];
+
+static int sm_count() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (g_sm_count[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        g_sm_count[dev] = n;
+    }
+    return g_sm_count[dev];
+}
+
+// grid: every SM gets MINB resident CTAs (one full wave); never more CTAs than work.
+static int grid_for(int64_t work_items_per_thread_group, int minb) {
+    int64_t full = (int64_t)sm_count() * minb;
+    int64_t need = (work_items_per_thread_group + kThreads - 1) / kThreads;
+    if (need < 1) need = 1;
+    int64_t g = need < full ? need : full;
+    if (g > kMaxPartials) g = kMaxPartials;
+    return (int)g;
+}
+
+template <int U, int MINB, class Op>
+static int launch_flat(const Op& op, int64_t n, void* scratch, float* sum_out, cudaStream_t s) {
+    if (n == 0 && !Op::kHasSum) return ND_OK;
+    int grid = grid_for((n + 3) / 4, MINB);
+    flat_kernel<U, MINB, Op><<<grid, kThreads, 0, s>>>(op, n, static_cast<Scratch*>(scratch), sum_out);
+    return check_launch("flat_kernel");
+}
+
+template <int U, int MINB, class Op>
+static int launch_table(const Op& op, const nd_tensor_desc* tab, int T, int64_t chunks, void* scratch,
+                        float* sum_out, cudaStream_t s) {
+    if ((T == 0 || chunks == 0) && !Op::kHasSum) return ND_OK;
+    int64_t full = (int64_t)sm_count() * MINB;
+    int grid = (int)(chunks < full ? (chunks > 0 ? chunks : 1) : full);
+    if (grid > kMaxPartials) grid = kMaxPartials;
+    table_kernel<U, MINB, Op><<<grid, kThreads, 0, s>>>(op, tab, T, chunks, static_cast<Scratch*>(scratch), sum_out);
+    return check_launch("table_kernel");
+}
+
+static OuterHyper make_outer_hyper(float lr, float mu, float dampening, float wd, int nesterov, int first) {
+    OuterHyper h;
+    h.neg_lr = -lr; h.mu = mu; h.one_minus_damp = 1.0f - dampening; h.wd = wd;
+    h.nesterov = nesterov; h.first_step = first;
+    return h;
+}
+
+static AdamHyper make_adam_hyper(double lr, double b1, double b2, double eps, double wd, int64_t step,
+                                 float max_norm, int zero_grad) {
+    // mirrors the host arithmetic of torch:optim/adam.py:692,773-781 (double, then cast)
+    AdamHyper h;
+    h.decay = (float)(1.0 - lr * wd);
+    h.w1 = (float)(1.0 - b1);
+    h.b2 = (float)b2;
+    h.w2 = (float)(1.0 - b2);
+    const double bc1 = 1.0 - std::pow(b1, (double)step);
+    const double bc2 = 1.0 - std::pow(b2, (double)step);
+    h.step_size = (float)((lr / bc1) * -1.0);
+    h.bc2_sqrt = (float)std::sqrt(bc2);
+    h.eps = (float)eps;
+    h.max_norm = max_norm;
+    h.has_decay = wd != 0.0;
+    h.zero_grad = zero_grad;
+    return h;
+}
+
+// tuning knobs: groups in flight per thread / resident CTAs per SM
+constexpr int U_PG = 2, B_PG = 4;
+constexpr int U_SHARD = 2, B_SHARD = 3;
+constexpr int U_SUMSQ = 4, B_SUMSQ = 4;
+constexpr int U_ADAM = 1, B_ADAM = 3;
+
+template <int W, bool BF16, bool SUM>
+static int launch_fused(float* master, float* mom, void* const* locals, int w_rt, int64_t n, const OuterHyper& h,
+                        float* sumsq_out, void* scratch, cudaStream_t s) {
+    OuterFusedOp<W, BF16, SUM> op;
+    op.master = master; op.mom = mom; op.w_rt = w_rt; op.world = (float)w_rt; op.h = h; op.acc = 0.f;
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k < w_rt ? locals[k] : nullptr;
+    // registers: (2 + W) float4 per group; keep >= 1536 threads/SM while it fits
+    if constexpr (W == 1) return launch_flat<2, 3>(op, n, scratch, sumsq_out, s);
+    else if constexpr (W == 2) return launch_flat<2, 2>(op, n, scratch, sumsq_out, s);
+    else if constexpr (W > 0 && W <= 4) return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
+    else return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
+}
+
+template <bool BF16, bool SUM>
+static int dispatch_fused(int W, float* master, float* mom, void* const* locals, int64_t n, const OuterHyper& h,
+                          float* sumsq_out, void* scratch, cudaStream_t s) {
+    switch (W) {
+        case 1: return launch_fused<1, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        case 2: return launch_fused<2, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        case 3: return launch_fused<3, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        case 4: return launch_fused<4, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        case 8: return launch_fused<8, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        default: return launch_fused<0, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+    }
+}
+
+}  // namespace nd
+
+using namespace nd;
+
+// ===========================================================================
+// C ABI
+// ===========================================================================
+
+#define ND_REQUIRE(cond, msg)                       \
+    do {                                            \
+        if (!(cond)) return set_error(ND_EINVAL, "%s: %s", __func__, msg); \
+    } while (0)
+
+extern "C" {
+
+int nd_version(void) { return 100; }
+
+const char* nd_last_error(void) { return nd::last_error(); }
+
+size_t nd_scratch_bytes(void) { return sizeof(Scratch); }
+
+int nd_pseudo_grad(const float* master, const void* local, int local_dtype, float* pg, int64_t n,
+                   nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(n == 0 || (master && local && pg), "null pointer");
+    ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (local_dtype == ND_BF16) {
+        PseudoGradOp<true> op{master, local, pg};
+        return launch_flat<U_PG, B_PG>(op, n, nullptr, nullptr, s);
+    }
+    PseudoGradOp<false> op{master, local, pg};
+    return launch_flat<U_PG, B_PG>(op, n, nullptr, nullptr, s);
+}
+
+int nd_pseudo_grad_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int local_dtype,
+                      nd_stream_t stream) {
+    ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
+    ND_REQUIRE(n_tensors == 0 || table_dev, "null table");
+    ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (local_dtype == ND_BF16) {
+        PseudoGradOp<true> op{nullptr, nullptr, nullptr};
+        return launch_table<U_PG, B_PG>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
+    }
+    PseudoGradOp<false> op{nullptr, nullptr, nullptr};
+    return launch_table<U_PG, B_PG>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
+}
+
+int nd_outer_nesterov(float* master, float* mom, const float* pg_sum, void* local_out, int local_dtype, int64_t n,
+                      float world, float lr, float mu, float dampening, float wd, int nesterov, int first_step,
+                      float* sumsq_out, void* scratch, nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(n == 0 || (master && mom && pg_sum), "null pointer");
+    ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
+    ND_REQUIRE(world >= 1.0f, "world < 1");
+    ND_REQUIRE(!sumsq_out || scratch, "sumsq_out needs scratch");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
+#define ND_SHARD(BF, SM)                                                                     \
+    do {                                                                                     \
+        OuterShardOp<BF, SM> op;                                                             \
+        op.master = master; op.mom = mom; op.pg_sum = pg_sum; op.local_out = local_out;      \
+        op.world = world; op.h = h; op.acc = 0.f;                                            \
+        return launch_flat<U_SHARD, B_SHARD>(op, n, scratch, sumsq_out, s);                  \
+    } while (0)
+    if (local_dtype == ND_BF16) { if (sumsq_out) ND_SHARD(true, true); else ND_SHARD(true, false); }
+    if (sumsq_out) ND_SHARD(false, true); else ND_SHARD(false, false);
+#undef ND_SHARD
+}
+
+int nd_outer_fused(float* master, float* mom, void* const* locals_host, int W, int local_dtype, int64_t n, float lr,
+                   float mu, float dampening, float wd, int nesterov, int first_step, float* sumsq_out,
+                   void* scratch, nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(W >= 1 && W <= ND_MAX_WORKERS, "W out of range [1, ND_MAX_WORKERS]");
+    ND_REQUIRE(locals_host, "null locals_host");
+    ND_REQUIRE(n == 0 || (master && mom), "null pointer");
+    for (int k = 0; k < W; ++k) ND_REQUIRE(n == 0 || locals_host[k], "null local pointer");
+    ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
+    ND_REQUIRE(!sumsq_out || scratch, "sumsq_out needs scratch");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
+    if (local_dtype == ND_BF16) {
+        return sumsq_out ? dispatch_fused<true, true>(W, master, mom, locals_host, n, h, sumsq_out, scratch, s)
+                         : dispatch_fused<true, false>(W, master, mom, locals_host, n, h, nullptr, nullptr, s);
+    }
+    return sumsq_out ? dispatch_fused<false, true>(W, master, mom, locals_host, n, h, sumsq_out, scratch, s)
+                     : dispatch_fused<false, false>(W, master, mom, locals_host, n, h, nullptr, nullptr, s);
+}
+
+int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int local_dtype,
+                      float lr, float mu, float dampening, float wd, int nesterov, int first_step,
+                      nd_stream_t stream) {
+    ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
+    ND_REQUIRE(n_tensors == 0 || table_dev, "null table");
+    ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
+    if (local_dtype == ND_BF16) {
+        OuterFusedOp<1, true, false> op;
+        op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f;
+        return launch_table<2, 3>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
+    }
+    OuterFusedOp<1, false, false> op;
+    op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f;
+    return launch_table<2, 3>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
+}
+
+int nd_sumsq(const void* g, int dtype, int64_t n, float* out, void* scratch, nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE((n == 0 || g) && out && scratch, "null pointer");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    if (dtype == ND_BF16) {
+        SumsqOp<true> op{g, 0.f};
+        return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, scratch, out, s);
+    }
+    SumsqOp<false> op{g, 0.f};
+    return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, scratch, out, s);
+}
+
+int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, float* out, void* scratch,
+                nd_stream_t stream) {
+    ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
+    ND_REQUIRE((n_tensors == 0 || table_dev) && out && scratch, "null pointer");
+    SumsqOp<false> op{nullptr, 0.f};
+    return launch_table<U_SUMSQ, B_SUMSQ>(op, table_dev, n_tensors, total_chunks, scratch, out,
+                                          reinterpret_cast<cudaStream_t>(stream));
+}
+
+int nd_adamw(float* p, float* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2, double eps,
+             double weight_decay, int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
+             nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(n == 0 || (p && g && m && v), "null pointer");
+    ND_REQUIRE(step >= 1, "step must be >= 1 (1-based)");
+    AdamWOp op;
+    op.p = p; op.g = g; op.m = m; op.v = v; op.sumsq = sumsq_dev; op.coef = 1.f;
+    op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+    return launch_flat<U_ADAM, B_ADAM>(op, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, double lr, double beta1,
+                double beta2, double eps, double weight_decay, int64_t step, const float* sumsq_dev,
+                float max_norm, int zero_grad, nd_stream_t stream) {
+    ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
+    ND_REQUIRE(n_tensors == 0 || table_dev, "null table");
+    ND_REQUIRE(step >= 1, "step must be >= 1 (1-based)");
+    AdamWOp op;
+    op.p = op.g = op.m = op.v = nullptr; op.sumsq = sumsq_dev; op.coef = 1.f;
+    op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+    return launch_table<U_ADAM, B_ADAM>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr,
+                                        reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,313 @@
+"""Drop-in `Diloco` wrapper whose hot path runs on hand-written sm_100a kernels.
+
+Mirrors the reference class `Diloco` (nanodiloco/diloco/diloco.py:7-74): same
+constructor signature, same methods (`outer_step`, `inner_step`, `__call__`,
+`train`, `eval`), same attributes read by the training loop (`model`,
+`inner_optimizer`, `outer_optimizer`, `scheduler`,
+`offloaded_last_sync_parameters`, `avg_sync_time`).  The caller still builds a
+stock `torch.optim.AdamW` and `torch.optim.SGD(momentum=0.9, nesterov=True)`
+(nanodiloco/main.py:100-101) and hands them in; their `param_groups` are read on
+every step (so schedulers keep working) and their `state` is populated with
+views into the flat buffers (so `state_dict()` keeps working).
+
+What changes underneath:
+  * parameters, last-sync master copy, outer momentum, gradients and AdamW
+    moments live in flat, 16-byte-aligned HBM buffers; `param.data` is re-homed
+    once and never rebound (diloco.py:50 rebinds it each outer step);
+  * the last-sync copy stays in HBM: the two PCIe crossings of diloco.py:29,47
+    are gone;
+  * `outer_step` is one fused kernel at world size 1, and a bucketed
+    reduce-scatter -> fused update -> all-gather pipeline otherwise;
+  * `inner_step` is a sum-of-squares pass plus one fused clip+AdamW pass, with
+    the clip coefficient computed on the device (no host synchronisation).
+
+There is no CPU path: constructing this class with CPU parameters raises.
+"""
+from __future__ import annotations
+
+import math
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from .flat import FlatLayout, rehome_
+
+
+def _cosine_schedule_with_warmup(optimizer, num_warmup_steps: int, num_training_steps: int):
+    """Same multiplier as transformers.get_cosine_schedule_with_warmup(num_cycles=0.5),
+    which the reference calls at diloco.py:20; restated so that importing this
+    module does not import transformers."""
+
+    def lr_lambda(current_step: int) -> float:
+        if current_step < num_warmup_steps:
+            return float(current_step) / float(max(1, num_warmup_steps))
+        progress = float(current_step - num_warmup_steps) / float(max(1, num_training_steps - num_warmup_steps))
+        return max(0.0, 0.5 * (1.0 + math.cos(math.pi * 0.5 * 2.0 * progress)))
+
+    return torch.optim.lr_scheduler.LambdaLR(optimizer, lr_lambda, -1)
+
+
+def _flatten_groups(optimizer) -> List[torch.nn.Parameter]:
+    return [p for g in optimizer.param_groups for p in g["params"]]
+
+
+class Diloco:
+    def __init__(
+        self,
+        model,
+        inner_optimizer,
+        outer_optimizer,
+        warmup_steps,
+        total_steps,
+        inner_steps: int = 100,
+        outer_steps: int = 10,
+        *,
+        bucket_mb: float = 64.0,
+        n_streams: int = 2,
+        process_group=None,
+        fused_inner: bool = True,
+        max_grad_norm: float = 1.0,
+    ):
+        # diloco.py:17-20
+        self.model = model
+        self.inner_optimizer = inner_optimizer
+        self.outer_optimizer = outer_optimizer
+        self.scheduler = _cosine_schedule_with_warmup(self.inner_optimizer, warmup_steps, total_steps)
+        self.inner_steps = inner_steps   # accepted and unused, as in the reference (diloco.py:14-15)
+        self.outer_steps = outer_steps
+        self.max_grad_norm = max_grad_norm
+        self.fused_inner = fused_inner
+
+        self._pg_group = process_group
+        self.world_size = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
+        self.rank = dist.get_rank(process_group) if self.world_size > 1 else 0
+
+        # The reference snapshots from outer_optimizer.param_groups (diloco.py:27-32) but zips the
+        # snapshot against inner_optimizer.param_groups (diloco.py:40-46); both must enumerate the
+        # same parameters in the same order.  Here that is checked instead of assumed.
+        self._params = _flatten_groups(outer_optimizer)
+        inner_params = _flatten_groups(inner_optimizer)
+        if len(inner_params) != len(self._params) or any(a is not b for a, b in zip(inner_params, self._params)):
+            raise ValueError("inner and outer optimizers must hold the same parameters in the same order")
+        if not self._params:
+            raise ValueError("no parameters to synchronise")
+        dev = self._params[0].device
+        if dev.type != "cuda":
+            raise _lib.NDError("nanodiloco_b200.Diloco needs CUDA parameters: the hot path is sm_100a kernels, "
+                               "there is no CPU implementation")
+        for p in self._params:
+            if p.device != dev:
+                raise ValueError("all parameters must live on one device")
+            if p.dtype != torch.float32:
+                raise ValueError(f"parameters must be float32 like the reference's (got {p.dtype})")
+        self.device = dev
+        _lib.load()
+
+        # ---- flat buffers ---------------------------------------------------------------------
+        W = self.world_size
+        self.layout = FlatLayout.plan(self._params, quantum=4 * W)
+        n = self.layout.total
+        self._local = torch.zeros(n, dtype=torch.float32, device=dev)
+        rehome_(self._params, self._local, self.layout)
+
+        # diloco.py:21-22: every worker starts from rank 0's parameters (one flat broadcast
+        # instead of one per tensor)
+        if W > 1:
+            dist.broadcast(self._local, src=dist.get_global_rank(process_group, 0) if process_group else 0,
+                           group=process_group)
+
+        # diloco.py:25: theta_sync, kept in HBM
+        self._master = self._local.clone()
+        self._first_outer = True
+        self._scratch = _lib.scratch(dev)
+
+        # ---- sharded sync context -------------------------------------------------------------
+        self._ctx = None
+        if W > 1:
+            from .sync import SyncContext
+            self._ctx = SyncContext(W, self.rank, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
+                                    n_streams=n_streams, group=process_group, device=dev)
+            self._mom = torch.zeros(self._ctx.shard_elems(n), dtype=torch.float32, device=dev)
+            self._pg = torch.empty(n, dtype=torch.float32, device=dev)
+        else:
+            self._mom = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._pg = None
+
+        # ---- inner optimizer state in flat buffers --------------------------------------------
+        self._grad = None
+        self._inner_step_count = 0
+        if fused_inner:
+            self._grad = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
+            self._grad_views = self.layout.views(self._grad)
+            self._attach_grads()
+            # same keys torch.optim.AdamW creates lazily (torch:optim/adam.py:167-190)
+            for p, m, v in zip(self._params, self.layout.views(self._exp_avg), self.layout.views(self._exp_avg_sq)):
+                st = self.inner_optimizer.state[p]
+                if len(st) == 0:
+                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
+                    st["exp_avg"] = m
+                    st["exp_avg_sq"] = v
+                else:  # caller resumed an optimizer: adopt its moments
+                    m.copy_(st["exp_avg"]); v.copy_(st["exp_avg_sq"])
+                    st["exp_avg"], st["exp_avg_sq"] = m, v
+                    self._inner_step_count = int(st["step"])
+            self._inner_ranges = self._group_ranges(self.inner_optimizer)
+        self._outer_ranges = self._group_ranges(self.outer_optimizer)
+
+        # diloco.py:23-24 declares these and never updates them; here they are real
+        self._sync_time = 0.0
+        self._sync_calls = 0
+        self._pending_events: List[tuple] = []
+
+    # ------------------------------------------------------------------------------------------
+    def _group_ranges(self, optimizer):
+        """(group, start, end) element ranges of each param group in the flat space."""
+        out, i = [], 0
+        for g in optimizer.param_groups:
+            k = len(g["params"])
+            if k:
+                s, e = self.layout.span(i, i + k - 1)
+                out.append((g, s, e))
+            i += k
+        if out:  # the tail padding rides with the last group (zeros stay zeros)
+            g, s, _ = out[-1]
+            out[-1] = (g, s, self.layout.total)
+        return out
+
+    def _attach_grads(self) -> None:
+        for p, gv in zip(self._params, self._grad_views):
+            p.grad = gv
+
+    @property
+    def offloaded_last_sync_parameters(self) -> List[torch.Tensor]:
+        """theta_sync per tensor (diloco.py:25,54) -- views of the HBM-resident master copy."""
+        return self.layout.views(self._master)
+
+    def _get_offloaded_parameters(self):  # diloco.py:27-32, for callers that used it
+        return [t.detach().clone().to("cpu") for t in self.offloaded_last_sync_parameters]
+
+    # ------------------------------------------------------------------------------------------
+    def outer_step(self) -> None:
+        """The DiLoCo outer synchronisation (diloco.py:34-54) on the GPU.
+
+        pseudo-gradient (master - local) -> average over workers -> Nesterov SGD on the
+        master copy -> copy the new parameters into every worker, with the hyper-parameters
+        read from `outer_optimizer.param_groups` at call time."""
+        stream = torch.cuda.current_stream(self.device)
+        t0 = torch.cuda.Event(enable_timing=True)
+        t1 = torch.cuda.Event(enable_timing=True)
+        t0.record(stream)
+        first = self._first_outer
+        if self._ctx is None:
+            for g, s, e in self._outer_ranges:
+                self._check_outer_group(g)
+                _lib.outer_fused(self._master[s:e], self._mom[s:e], [self._local[s:e]],
+                                 lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                 dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
+                                 nesterov=bool(g["nesterov"]), first_step=first)
+        else:
+            if len(self._outer_ranges) != 1:
+                raise NotImplementedError("the sharded outer sync supports a single outer param group")
+            g = self._outer_ranges[0][0]
+            self._check_outer_group(g)
+            self._ctx.outer_sync(self._local, self._master, self._mom, self._pg,
+                                 lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                 dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
+                                 nesterov=bool(g["nesterov"]), first_step=first)
+        t1.record(stream)
+        self._pending_events.append((t0, t1))
+        self._first_outer = False
+        self._publish_outer_state()
+        # diloco.py:53 -- outer_optimizer.zero_grad(): the pseudo-gradient never became .grad here
+
+    @staticmethod
+    def _check_outer_group(g) -> None:
+        if g.get("maximize", False):
+            raise NotImplementedError("outer SGD with maximize=True is not supported")
+
+    def _publish_outer_state(self) -> None:
+        """outer_optimizer.state[p]['momentum_buffer'] as views (world size 1).  With the
+        sharded sync each rank holds 1/W of the momentum; `gather_outer_state()` assembles it."""
+        if self._ctx is not None:
+            return
+        for p, v in zip(self._params, self.layout.views(self._mom)):
+            self.outer_optimizer.state[p]["momentum_buffer"] = v
+
+    def gather_outer_state(self) -> None:
+        """Collective: materialise the full momentum buffers into outer_optimizer.state."""
+        if self._ctx is None:
+            return self._publish_outer_state()
+        full = self._ctx.gather_shards(self._mom, self.layout.total)
+        for p, v in zip(self._params, self.layout.views(full)):
+            self.outer_optimizer.state[p]["momentum_buffer"] = v
+
+    # ------------------------------------------------------------------------------------------
+    def inner_step(self):
+        """diloco.py:56-60: clip_grad_norm_(1.0) -> AdamW step -> scheduler step -> zero_grad."""
+        if not self.fused_inner:
+            torch.nn.utils.clip_grad_norm_(self.model.parameters(), max_norm=self.max_grad_norm)
+            self.inner_optimizer.step()
+            self.scheduler.step()
+            self.inner_optimizer.zero_grad()
+            return
+        flat_ok = all(p.grad is not None and p.grad.data_ptr() == gv.data_ptr()
+                      for p, gv in zip(self._params, self._grad_views))
+        if not flat_ok:
+            self._adopt_foreign_grads()
+        self._inner_step_count += 1
+        _lib.sumsq(self._grad, self._sumsq, self._scratch)
+        for g, s, e in self._inner_ranges:
+            if g.get("amsgrad", False) or g.get("maximize", False):
+                raise NotImplementedError("fused inner AdamW does not support amsgrad/maximize")
+            b1, b2 = g["betas"]
+            _lib.adamw(self._local[s:e], self._grad[s:e], self._exp_avg[s:e], self._exp_avg_sq[s:e],
+                       lr=float(g["lr"]), beta1=float(b1), beta2=float(b2), eps=float(g["eps"]),
+                       weight_decay=float(g["weight_decay"]), step=self._inner_step_count,
+                       sumsq_dev=self._sumsq, max_norm=self.max_grad_norm, zero_grad=True)
+        for p in self._params:
+            self.inner_optimizer.state[p]["step"] += 1
+        self.scheduler.step()
+        # diloco.py:60 zero_grad(): fused into the AdamW pass; .grad stays a (zeroed) view of the
+        # flat gradient buffer so the next backward accumulates straight into it.
+
+    def _adopt_foreign_grads(self) -> None:
+        """A caller (or autograd after `zero_grad(set_to_none=True)`) replaced some `.grad`:
+        fold those gradients into the flat buffer and re-attach the views."""
+        with torch.no_grad():
+            for p, gv in zip(self._params, self._grad_views):
+                if p.grad is None:
+                    gv.zero_()
+                elif p.grad.data_ptr() != gv.data_ptr():
+                    gv.copy_(p.grad)
+        self._attach_grads()
+
+    @property
+    def last_grad_norm(self) -> torch.Tensor:
+        """Total gradient norm of the last inner step (device tensor; reading it synchronises)."""
+        return self._sumsq.sqrt()
+
+    # ------------------------------------------------------------------------------------------
+    @property
+    def avg_sync_time(self):
+        """Mean device time of `outer_step` in seconds (diloco.py:62-64 promises this and always
+        returns 0 because `_sync_time` is never updated there)."""
+        for t0, t1 in self._pending_events:
+            t1.synchronize()
+            self._sync_time += t0.elapsed_time(t1) / 1e3
+            self._sync_calls += 1
+        self._pending_events.clear()
+        return self._sync_time / self._sync_calls if self._sync_calls > 0 else 0
+
+    def __call__(self, *args, **kwargs):
+        return self.model(*args, **kwargs)
+
+    def train(self):
+        self.model.train()
+
+    def eval(self):
+        self.model.eval()

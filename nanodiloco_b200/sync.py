@@ -1,0 +1,94 @@
+"""Host side of the sharded multi-GPU outer sync (one process per GPU).
+
+`SyncContext` owns an `nd_sync_ctx` (include/nanodiloco_b200.h): an NCCL
+communicator of its own over the ranks of a torch process group, side streams
+and events.  torch.distributed is used only as plumbing -- to hand the NCCL
+unique id from rank 0 to the other ranks.  It replaces, for this path, the
+process group the reference creates at nanodiloco/training_utils/utils.py:41-43
+and uses per tensor at nanodiloco/diloco/diloco.py:49.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+
+def shard_index_map(n_padded: int, world: int, rank: int, bucket: int) -> torch.Tensor:
+    """Global element index of every element of `rank`'s shard, in shard order.
+
+    Bucket b covers [b*bucket, min((b+1)*bucket, n_padded)); it is cut into `world` equal
+    slices and rank r owns slice r.  Pure host logic (CPU tensor), shared with the tests."""
+    parts = []
+    off = 0
+    while off < n_padded:
+        length = min(bucket, n_padded - off)
+        assert length % world == 0
+        sl = length // world
+        parts.append(torch.arange(off + rank * sl, off + (rank + 1) * sl, dtype=torch.int64))
+        off += length
+    return torch.cat(parts) if parts else torch.zeros(0, dtype=torch.int64)
+
+
+class SyncContext:
+    def __init__(self, world: int, rank: int, *, bucket_elems: int, n_streams: int = 2, group=None,
+                 device=None):
+        L = _lib.load()
+        self.world, self.rank, self.group = world, rank, group
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        uid = ctypes.create_string_buffer(_lib.ND_UNIQUE_ID_BYTES)
+        if world > 1:
+            if rank == 0:
+                _lib.check(L.nd_nccl_unique_id(uid), "nd_nccl_unique_id")
+            box = [uid.raw]
+            src = dist.get_global_rank(group, 0) if group is not None else 0
+            dist.broadcast_object_list(box, src=src, group=group)
+            uid = ctypes.create_string_buffer(box[0], _lib.ND_UNIQUE_ID_BYTES)
+        handle = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(L.nd_sync_ctx_create(uid, world, rank, int(bucket_elems), int(n_streams),
+                                            ctypes.byref(handle)), "nd_sync_ctx_create")
+        self._h = handle
+        self.bucket = int(L.nd_sync_bucket_elems(self._h))
+
+    def padded_elems(self, n: int) -> int:
+        return int(_lib.load().nd_sync_padded_elems(self._h, n))
+
+    def shard_elems(self, n: int) -> int:
+        return int(_lib.load().nd_sync_shard_elems(self._h, n))
+
+    def outer_sync(self, local, master, mom_shard, pg, *, lr, momentum, dampening=0.0, weight_decay=0.0,
+                   nesterov=True, first_step=False, stream=None) -> None:
+        _lib._require_cuda(local, master, mom_shard, pg)
+        _lib.check(_lib.load().nd_outer_sync(self._h, _lib._ptr(local), _lib._ptr(master), _lib._ptr(mom_shard),
+                                             _lib._ptr(pg), local.numel(), lr, momentum, dampening, weight_decay,
+                                             int(nesterov), int(first_step), _lib._stream(stream)),
+                   "nd_outer_sync")
+
+    def last_ms(self) -> float:
+        ms = ctypes.c_float()
+        _lib.check(_lib.load().nd_sync_last_ms(self._h, ctypes.byref(ms)), "nd_sync_last_ms")
+        return float(ms.value)
+
+    def gather_shards(self, shard: torch.Tensor, n_padded: int) -> torch.Tensor:
+        """Collective over the torch group: the full flat buffer assembled from every rank's shard."""
+        parts = [torch.empty_like(shard) for _ in range(self.world)]
+        dist.all_gather(parts, shard, group=self.group)
+        full = torch.empty(n_padded, dtype=shard.dtype, device=shard.device)
+        for r, part in enumerate(parts):
+            full[shard_index_map(n_padded, self.world, r, self.bucket).to(shard.device)] = part
+        return full
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            _lib.load().nd_sync_ctx_destroy(self._h)
+            self._h = None
+
+    def __del__(self):  # pragma: no cover
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -1,0 +1,125 @@
+"""GPU parity of the inner-step kernels (sum of squares, fused clip + AdamW) through the C ABI."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from nanodiloco_b200 import _lib
+from oracle import oracle as O
+from gpu_util import dev, host, unaligned
+
+pytestmark = pytest.mark.gpu
+
+
+def _rand(n, seed, scale):
+    return (np.random.default_rng(seed).standard_normal(n) * scale).astype(np.float32)
+
+
+@pytest.mark.parametrize("n", [0, 1, 3, 5, 4096, 1_000_003, 30_000_001])
+def test_sumsq_vs_oracle_and_deterministic(n):
+    g_np = _rand(n, 5, 0.05)
+    g = dev(g_np)
+    sc = _lib.scratch("cuda")
+    out = torch.full((2,), float("nan"), device="cuda")
+    _lib.sumsq(g, out[0:1], sc)
+    _lib.sumsq(g, out[1:2], sc)                     # scratch is reusable without re-zeroing
+    a, b = out.tolist()
+    assert a == b                                   # fixed reduction order: bit-identical reruns
+    assert a == pytest.approx(O.sumsq(g_np), rel=2e-6, abs=0)
+    if n:
+        _lib.sumsq(unaligned(g), out[0:1], sc)      # scalar path
+        assert float(out[0]) == pytest.approx(O.sumsq(g_np), rel=2e-6)
+
+
+def test_sumsq_bf16_and_multi_tensor():
+    g16 = torch.from_numpy(_rand(70_001, 6, 0.05)).to(torch.bfloat16).cuda()
+    sc = _lib.scratch("cuda")
+    out = torch.zeros(1, device="cuda")
+    _lib.sumsq(g16, out, sc)
+    assert float(out) == pytest.approx(O.sumsq(g16.float().cpu().numpy()), rel=2e-6)
+    ts = [dev(_rand(s, 20 + i, 0.05)) for i, s in enumerate([128, 7, 16385, 1, 40_000])]
+    tab, T, chunks = _lib.make_table([(t,) for t in ts], "cuda")
+    _lib.check(_lib.load().nd_sumsq_mt(tab.data_ptr(), T, chunks, out.data_ptr(), sc.data_ptr(), _lib._stream()))
+    want = sum(O.sumsq(host(t)) for t in ts)
+    assert float(out) == pytest.approx(want, rel=2e-6)
+
+
+@pytest.mark.parametrize("n", [1, 7, 4099, 1_000_003])
+@pytest.mark.parametrize("scale", [0.05, 1e-4])          # clipping active / inactive
+def test_adamw_bit_exact_vs_oracle_cuda_recipe(n, scale):
+    p_np, m_np, v_np = _rand(n, 1, 0.02), _rand(n, 2, 1e-3), np.abs(_rand(n, 3, 1e-6))
+    p, m, v = dev(p_np), dev(m_np), dev(v_np)
+    sc = _lib.scratch("cuda")
+    ss = torch.zeros(1, device="cuda")
+    for step in range(1, 4):
+        g_np = _rand(n, 10 + step, scale)
+        g = dev(g_np)
+        _lib.sumsq(g, ss, sc)
+        _lib.adamw(p, g, m, v, lr=4e-4, step=step, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
+        coef = O.clip_coef(float(np.sqrt(np.float32(float(ss)))), 1.0)   # same fp32 sqrt as the kernel
+        O.adamw_step(p_np, g_np, m_np, v_np, lr=4e-4, step=step, clip=coef, recipe="cuda")
+        assert np.array_equal(host(m), m_np) and np.array_equal(host(v), v_np), step
+        assert np.array_equal(host(p), p_np), step
+        assert float(g.abs().max()) == 0.0                                # fused zero_grad (diloco.py:60)
+
+
+def test_adamw_vs_torch_cuda_foreach():
+    """What the reference executes on a GPU (diloco.py:57-58): clip_grad_norm_ + AdamW.step()."""
+    sizes = [4096, 7, 100_000, 333]
+    gen = torch.Generator(device="cuda").manual_seed(0)
+    ref = [torch.nn.Parameter(torch.randn(s, device="cuda", generator=gen) * 0.02) for s in sizes]
+    opt = torch.optim.AdamW(ref, lr=4e-4)
+    n = sum(sizes)
+    p = torch.cat([r.data.reshape(-1) for r in ref]).clone()
+    m, v, ss = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(1, device="cuda")
+    sc = _lib.scratch("cuda")
+    for step in range(1, 6):
+        scale = 0.05 if step % 2 else 1e-4
+        grads = [torch.randn(s, device="cuda", generator=gen) * scale for s in sizes]
+        for r, g in zip(ref, grads):
+            r.grad = g.clone()
+        total = torch.nn.utils.clip_grad_norm_(ref, max_norm=1.0)
+        opt.step()
+        g = torch.cat(grads)
+        _lib.sumsq(g, ss, sc)
+        _lib.adamw(p, g, m, v, lr=4e-4, step=step, sumsq_dev=ss, max_norm=1.0)
+        assert float(ss.sqrt()) == pytest.approx(float(total), rel=2e-6)
+        want_p = torch.cat([r.data for r in ref])
+        want_m = torch.cat([opt.state[r]["exp_avg"] for r in ref])
+        want_v = torch.cat([opt.state[r]["exp_avg_sq"] for r in ref])
+        # the clip coefficient differs by an ulp (different reduction order for the norm), so:
+        # fp32 tolerance rtol 2e-6 with an atol floor of 1e-6 * max|x|
+        for got, want in ((p, want_p), (m, want_m), (v, want_v)):
+            torch.testing.assert_close(got, want, rtol=2e-6, atol=1e-6 * float(want.abs().max()))
+
+
+def test_adamw_vs_reference_golden(golden_dir):
+    z = np.load(os.path.join(golden_dir, "inner.npz"))
+    p, n = dev(z["init"]), z["init"].size
+    m, v, ss = torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda"), torch.zeros(1, device="cuda")
+    sc = _lib.scratch("cuda")
+    for s in range(6):
+        g = dev(z[f"grad_s{s}"])
+        _lib.sumsq(g, ss, sc)
+        assert float(ss.sqrt()) == pytest.approx(float(z[f"total_norm_s{s}"]), rel=2e-6)
+        _lib.adamw(p, g, m, v, lr=float(z[f"lr_s{s}"]), step=s + 1, sumsq_dev=ss, max_norm=1.0)
+        for got, key in ((p, "params"), (m, "exp_avg"), (v, "exp_avg_sq")):
+            want = z[f"{key}_s{s}"]
+            np.testing.assert_allclose(host(got), want, rtol=2e-6, atol=1e-6 * np.abs(want).max())
+
+
+def test_adamw_multi_tensor_matches_flat():
+    sizes = [128, 7, 16385, 1, 40_000]
+    mk = lambda seed, sc: [dev(_rand(s, seed + i, sc)) for i, s in enumerate(sizes)]
+    ps, gs, ms, vs = mk(0, 0.02), mk(10, 0.01), mk(20, 1e-3), [t.abs() for t in mk(30, 1e-6)]
+    want = []
+    for p, g, m, v in zip(ps, gs, ms, vs):
+        p2, m2, v2 = p.clone(), m.clone(), v.clone()
+        _lib.adamw(p2, g.clone(), m2, v2, lr=1e-3, step=3, max_norm=1.0)
+        want.append((p2, m2, v2))
+    tab, T, chunks = _lib.make_table(list(zip(ps, gs, ms, vs)), "cuda")
+    _lib.check(_lib.load().nd_adamw_mt(tab.data_ptr(), T, chunks, 1e-3, 0.9, 0.999, 1e-8, 1e-2, 3, None, 1.0, 0,
+                                       _lib._stream()))
+    for (p2, m2, v2), p, m, v in zip(want, ps, ms, vs):
+        assert torch.equal(p, p2) and torch.equal(m, m2) and torch.equal(v, v2)

@@ -1,0 +1,73 @@
+"""GPU, world size >= 2 (skipped on a single-GPU box): the sharded outer sync over NCCL
+(nd_outer_sync: K1 -> reduce-scatter -> K2 on the owned slice -> all-gather, bucketed) through the
+drop-in wrapper, against the reference's golden fixtures."""
+import os
+import tempfile
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _worker(rank, world, store, bucket_mb, result_path):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from test_gpu_diloco import Bag, _flat
+    from nanodiloco_b200 import Diloco
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", init_method=f"file://{store}", rank=rank, world_size=world,
+                            device_id=torch.device("cuda", rank))
+    z = np.load(os.path.join(GOLDEN, f"outer_w{world}.npz"))
+    model = Bag(z["init"]).cuda()
+    if rank != 0:                                   # diloco.py:21-22: rank 0's parameters win
+        with torch.no_grad():
+            for p in model.parameters():
+                p.add_(1.0)
+    inner = torch.optim.AdamW(model.parameters(), lr=4e-4)
+    outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2)
+    params = list(model.parameters())
+    ok = np.array_equal(_flat(params).cpu().numpy(), z["init"])
+    exact = world <= 2
+    for r in range(3):
+        loc = z[f"local_r{r}_w{rank}"]
+        off = 0
+        with torch.no_grad():
+            for p in params:
+                p.copy_(torch.from_numpy(loc[off:off + p.numel()]).reshape(p.shape))
+                off += p.numel()
+        d.outer_step()
+        got = _flat(params).cpu().numpy()
+        want = z[f"params_r{r}"]
+        d.gather_outer_state()
+        mom = _flat([outer.state[p]["momentum_buffer"] for p in params]).cpu().numpy()
+        if exact:
+            ok &= np.array_equal(got, want) and np.array_equal(mom, z[f"mom_r{r}"])
+        else:
+            ok &= np.allclose(got, want, rtol=1e-6, atol=1e-6 * np.abs(want).max())
+            ok &= np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max())
+        ok &= np.array_equal(_flat(d.offloaded_last_sync_parameters).cpu().numpy(), got)
+    ok &= d.avg_sync_time > 0
+    flag = torch.tensor([1 if ok else 0], device="cuda")
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        with open(result_path, "w") as f:
+            f.write("ok" if int(flag) == 1 else "mismatch")
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("bucket_mb", [0.002, 64.0])      # many tiny buckets / one bucket
+def test_sharded_outer_sync_vs_reference(world, bucket_mb):
+    if torch.cuda.device_count() < world:
+        pytest.skip(f"needs {world} GPUs")
+    with tempfile.TemporaryDirectory() as td:
+        res = os.path.join(td, "res")
+        mp.spawn(_worker, args=(world, os.path.join(td, "store"), bucket_mb, res), nprocs=world, join=True)
+        assert open(res).read() == "ok"

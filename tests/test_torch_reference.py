@@ -1,0 +1,113 @@
+"""CPU: pins oracle/torch_reference.py (the port bench.py times as the CPU baseline) against
+(a) the REAL reference class when /root/reference is mounted (build container only) and
+(b) the committed golden fixtures (always)."""
+import importlib.util
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle.torch_reference import CONFIGS, ReferenceDilocoPort, llama_shapes
+
+REF = "/root/reference/nanodiloco/diloco/diloco.py"
+SHAPES = [(128,), (64, 32), (1000,), (7,), (3, 5, 11), (1,), (2048,)]
+
+
+def _params(init):
+    ps, off = [], 0
+    for s in SHAPES:
+        n = int(np.prod(s))
+        ps.append(torch.nn.Parameter(torch.from_numpy(init[off:off + n].copy()).reshape(s)))
+        off += n
+    return ps
+
+
+def _flat(ts):
+    return torch.cat([t.detach().reshape(-1) for t in ts]).numpy()
+
+
+def _set(ps, flat):
+    off = 0
+    with torch.no_grad():
+        for p in ps:
+            p.copy_(torch.from_numpy(flat[off:off + p.numel()]).reshape(p.shape))
+            off += p.numel()
+
+
+def test_port_matches_golden_w1(golden_dir):
+    z = np.load(os.path.join(golden_dir, "outer_w1.npz"))
+    ps = _params(z["init"])
+    inner = torch.optim.AdamW(ps, lr=4e-4)
+    outer = torch.optim.SGD(ps, lr=0.7, momentum=0.9, nesterov=True)
+    d = ReferenceDilocoPort(ps, inner, outer, 2, 100)
+    for r in range(3):
+        _set(ps, z[f"local_r{r}_w0"])
+        d.outer_step()
+        assert np.array_equal(_flat(ps), z[f"params_r{r}"])
+        assert np.array_equal(_flat([outer.state[p]["momentum_buffer"] for p in ps]), z[f"mom_r{r}"])
+        assert all(p.grad is None for p in ps)
+
+
+def test_port_inner_matches_golden(golden_dir):
+    z = np.load(os.path.join(golden_dir, "inner.npz"))
+    ps = _params(z["init"])
+    inner = torch.optim.AdamW(ps, lr=4e-4)
+    outer = torch.optim.SGD(ps, lr=0.7, momentum=0.9, nesterov=True)
+    d = ReferenceDilocoPort(ps, inner, outer, 2, 10)
+    for s in range(6):
+        off = 0
+        for p in ps:
+            p.grad = torch.from_numpy(z[f"grad_s{s}"][off:off + p.numel()].copy()).reshape(p.shape)
+            off += p.numel()
+        d.inner_step()
+        assert np.array_equal(_flat(ps), z[f"params_s{s}"])
+        assert np.array_equal(_flat([inner.state[p]["exp_avg_sq"] for p in ps]), z[f"exp_avg_sq_s{s}"])
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="the reference is only mounted in the build container")
+def test_port_is_bit_identical_to_the_real_reference():
+    import torch.distributed as dist
+    import tempfile
+    spec = importlib.util.spec_from_file_location("ref_diloco", REF)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    with tempfile.TemporaryDirectory() as td:
+        dist.init_process_group("gloo", init_method=f"file://{td}/s", rank=0, world_size=1)
+        try:
+            g = torch.Generator().manual_seed(1337)
+            init = (torch.randn(sum(int(np.prod(s)) for s in SHAPES), generator=g) * 0.02).numpy()
+
+            class Bag(torch.nn.Module):
+                def __init__(self):
+                    super().__init__()
+                    self.ps = torch.nn.ParameterList(_params(init))
+
+            a = Bag()
+            ai = torch.optim.AdamW(a.parameters(), lr=4e-4)
+            ao = torch.optim.SGD(a.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+            ref = mod.Diloco(a, ai, ao, 2, 20)
+            bp = _params(init)
+            bi = torch.optim.AdamW(bp, lr=4e-4)
+            bo = torch.optim.SGD(bp, lr=0.7, momentum=0.9, nesterov=True)
+            port = ReferenceDilocoPort(bp, bi, bo, 2, 20)
+            for step in range(1, 9):
+                for i, (p, q) in enumerate(zip(a.parameters(), bp)):
+                    gg = torch.Generator().manual_seed(step * 100 + i)
+                    grad = torch.randn(p.shape, generator=gg) * (0.05 if step % 2 else 0.002)
+                    p.grad, q.grad = grad.clone(), grad.clone()
+                ref.inner_step(); port.inner_step()
+                if step % 4 == 0:
+                    ref.outer_step(); port.outer_step()
+                assert np.array_equal(_flat(a.parameters()), _flat(bp)), step
+        finally:
+            dist.destroy_process_group()
+
+
+def test_llama_shape_tables():
+    """tensor counts and element counts of the BASELINE model sizes."""
+    for name, (tensors, elems) in {"tiny": (57, 9_766_528), "llama150m": (111, 214_983_680),
+                                   "llama1b": (201, 1_261_529_088)}.items():
+        shapes = llama_shapes(**CONFIGS[name])
+        assert len(shapes) == tensors
+        assert sum(int(np.prod(s)) for s in shapes) == elems
