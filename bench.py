@@ -1,0 +1,418 @@
+#!/usr/bin/env python
+"""bench.py -- DiLoCo outer-sync benchmark (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl native|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One "step" = one DiLoCo outer synchronisation (pseudo-gradient -> cross-worker average ->
+Nesterov outer SGD -> copy-back; reference nanodiloco/diloco/diloco.py:34-54) over the flat
+fp32 parameter space of the 1B-class Llama of BASELINE.json configs[3] (201 tensors,
+1,261,529,088 parameters), every GPU holding one DiLoCo worker (weak scaling).
+
+Prints ONE JSON line (rank 0).  `value` = device milliseconds per outer sync with everything
+resident in HBM (max over ranks); `e2e` = the same step with the last-sync copy in HOST memory,
+where the reference keeps it (diloco.py:25-32,47,54), host<->device copies inside the timed
+region; `roofline` = the dominant kernel against the measured HBM copy bandwidth;
+`cpu_baseline` = the reference's CPU path (oracle/torch_reference.py port) on a bounded sample.
+
+`--impl reference` times only that CPU path, with all host threads, on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+OUTER_LR, OUTER_MU = 0.7, 0.9          # reference main.py:51, main.py:101
+METRIC, UNIT = "diloco_outer_sync_ms", "ms"
+WORKLOADS = {"llama1b": "llama1b", "llama150m": "llama150m", "tiny": "tiny"}
+
+
+def workload_shapes(name: str):
+    # shape tables only (no arithmetic): shared with the tests
+    from oracle.torch_reference import CONFIGS, llama_shapes
+    return llama_shapes(**CONFIGS[name])
+
+
+def numel(shape) -> int:
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks: sampled with NVML from a thread while the timed region runs
+# ---------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x1: "gpu_idle", 0x2: "applications_clocks_setting", 0x4: "sw_power_cap", 0x8: "hw_slowdown",
+               0x10: "sync_boost", 0x20: "sw_thermal_slowdown", 0x40: "hw_thermal_slowdown",
+               0x80: "hw_power_brake_slowdown", 0x100: "display_clock_setting"}
+
+    def __init__(self, index: int, period_s: float = 0.005):
+        self.samples, self.reason_bits, self.sm_max = [], 0, None
+        self._stop, self._active = threading.Event(), threading.Event()
+        self._thread, self._h, self._nv = None, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self._nv = pynvml
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = int(pynvml.nvmlDeviceGetMaxClockInfo(self._h, pynvml.NVML_CLOCK_SM))
+            self._period = period_s
+            self._thread = threading.Thread(target=self._run, daemon=True)
+            self._thread.start()
+        except Exception as e:  # noqa: BLE001
+            self.error = str(e)
+
+    def _run(self):
+        nv = self._nv
+        while not self._stop.is_set():
+            if self._active.is_set():
+                try:
+                    self.samples.append(int(nv.nvmlDeviceGetClockInfo(self._h, nv.NVML_CLOCK_SM)))
+                    self.reason_bits |= int(nv.nvmlDeviceGetCurrentClocksEventReasons(self._h))
+                except Exception:  # noqa: BLE001
+                    pass
+            time.sleep(self._period)
+
+    def start(self):
+        self._active.set()
+
+    def stop(self):
+        self._active.clear()
+
+    def close(self):
+        self._stop.set()
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.sm_max, "reasons": [], "samples": 0,
+                    "note": getattr(self, "error", "timed region shorter than one sample")}
+        reasons = [n for b, n in self.REASONS.items() if self.reason_bits & b and n != "gpu_idle"]
+        return {"sm_mhz": int(statistics.median(self.samples)), "sm_max_mhz": self.sm_max, "reasons": reasons,
+                "samples": len(self.samples)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the reference's CPU path (port), timed on the host cores
+# ---------------------------------------------------------------------------------------------
+def _cpu_worker(rank, world, store, shapes, threads, steps, warmup, out_path):
+    import torch
+    import torch.distributed as dist
+    from oracle.torch_reference import ReferenceDilocoPort
+    torch.set_num_threads(max(1, threads))
+    if world > 1:
+        dist.init_process_group("gloo", init_method=f"file://{store}", rank=rank, world_size=world)
+    g = torch.Generator().manual_seed(1337)
+    params = [torch.nn.Parameter(torch.randn(s, generator=g) * 0.02) for s in shapes]
+    inner = torch.optim.AdamW(params, lr=4e-4)
+    outer = torch.optim.SGD(params, lr=OUTER_LR, momentum=OUTER_MU, nesterov=True)
+    d = ReferenceDilocoPort(params, inner, outer, 100, 10_000)
+    gd = torch.Generator().manual_seed(100 + rank)
+    with torch.no_grad():
+        for p in params:
+            p.add_(torch.randn(p.shape, generator=gd) * 1e-3)
+    times = []
+    for i in range(warmup + steps):
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        d.outer_step()
+        if world > 1:
+            dist.barrier()
+        if i >= warmup:
+            times.append(time.perf_counter() - t0)
+    if rank == 0:
+        with open(out_path, "w") as f:
+            json.dump(times, f)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def time_reference_cpu(shapes, world: int, steps: int, warmup: int, threads_total: int):
+    """Seconds per outer step of the reference's CPU path on `shapes`, W=world gloo workers."""
+    import tempfile
+    import torch.multiprocessing as mp
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "times.json")
+        if world == 1:
+            _cpu_worker(0, 1, None, shapes, threads_total, steps, warmup, out)
+        else:
+            mp.spawn(_cpu_worker, args=(world, os.path.join(td, "store"), shapes, max(1, threads_total // world),
+                                        steps, warmup, out), nprocs=world, join=True)
+        return json.load(open(out))
+
+
+def host_cores() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:  # noqa: BLE001
+        return os.cpu_count() or 1
+
+
+def cpu_sample_shapes(all_shapes, budget_elems: int):
+    """A prefix of the model's tensor list (embedding + whole layers) within budget_elems."""
+    out, tot = [], 0
+    for s in all_shapes:
+        if out and tot + numel(s) > budget_elems:
+            break
+        out.append(s)
+        tot += numel(s)
+    return out, tot
+
+
+def run_cpu_baseline(all_shapes, n_total: int, world: int, steps: int, warmup: int, budget_s: float):
+    cores = host_cores()
+    # calibrate on a small prefix, then size the sample so that (steps+warmup) fits the budget
+    calib, calib_n = cpu_sample_shapes(all_shapes[1:], 30_000_000)   # a few layer tensors
+    t = min(time_reference_cpu(calib, world, 1, 1, cores))
+    per_elem = t / max(1, calib_n)
+    budget_elems = int(budget_s / max(1e-12, per_elem * (steps + warmup)))
+    # bounded sample: at most ~256M params (memory: ~6 fp32 copies live at once on the host)
+    shapes, sample_n = cpu_sample_shapes(all_shapes, min(max(budget_elems, 2_000_000), 256_000_000))
+    times = time_reference_cpu(shapes, world, steps, warmup, cores)
+    sec = statistics.median(times)
+    scale = n_total / sample_n
+    return {
+        "value": sec * 1e3 * scale, "unit": UNIT, "cores": cores, "kind": "port",
+        "sample": (f"oracle/torch_reference.py (statement-by-statement torch-CPU port of the reference's "
+                   f"Diloco.outer_step, {'gloo W=%d' % world if world > 1 else 'W=1'}) on the first {len(shapes)} "
+                   f"tensors = {sample_n} of {n_total} params; median of {steps} steps = {sec * 1e3:.1f} ms, "
+                   f"scaled x{scale:.2f} to the full model; torch threads = {cores}"),
+        "sample_ms": sec * 1e3, "sample_elems": sample_n,
+    }
+
+
+# ---------------------------------------------------------------------------------------------
+def reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    shapes = workload_shapes(args.workload)
+    n_total = sum(numel(s) for s in shapes)
+    steps, warmup = args.steps, max(1, args.warmup)
+    cb = run_cpu_baseline(shapes, n_total, args.gpus, steps, warmup, budget_s=args.cpu_budget_s)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": steps, "warmup": warmup, "ms_per_step": cb["value"], "higher_is_better": False,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, n_total, len(shapes), args.gpus),
+        "cpu_baseline": cb,
+        "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, n_total, n_tensors, world):
+    return {
+        "workload": (f"{args.workload} outer sync: {n_tensors} tensors, {n_total} fp32 params per worker, "
+                     f"outer SGD lr {OUTER_LR} momentum {OUTER_MU} nesterov, steady-state (momentum warmed), "
+                     f"{world} worker(s), 1 per GPU"),
+        "l2": "each step streams >= 15 GB per GPU (>> 126 MB L2): inputs larger than L2, no flush needed",
+        "parallelism": f"diloco-dp{world}",
+    }
+
+
+# ---------------------------------------------------------------------------------------------
+def native_arm(args):
+    import torch
+    import torch.distributed as dist
+    from nanodiloco_b200 import _lib
+    from nanodiloco_b200.flat import FlatLayout
+    from nanodiloco_b200.sync import SyncContext
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    _lib.load()
+
+    shapes = workload_shapes(args.workload)
+    metas = [torch.empty(s, device="meta") for s in shapes]
+    layout = FlatLayout.plan(metas, quantum=4 * world)
+    n_real = sum(numel(s) for s in shapes)
+    n = layout.total
+    K, Wm = args.steps, max(3, args.warmup)
+
+    g = torch.Generator(device=dev).manual_seed(0)
+    master = torch.empty(n, device=dev).normal_(0, 0.02, generator=g)
+    gl = torch.Generator(device=dev).manual_seed(100 + rank)
+    local = master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)
+    ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
+                      device=dev)
+    mom = torch.zeros(ctx.shard_elems(n), device=dev)
+    pg = torch.empty(n, device=dev) if world > 1 else None
+    hyper = dict(lr=OUTER_LR, momentum=OUTER_MU, dampening=0.0, weight_decay=0.0, nesterov=True)
+
+    def step(first=False):
+        ctx.outer_sync(local, master, mom, pg, first_step=first, **hyper)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    step(first=True)                                    # first-step branch, also warms the momentum
+    local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))   # drift again
+    for _ in range(Wm):
+        step()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+
+    # ---- timed region: exactly K steps ---------------------------------------------------------
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    if sampler:
+        sampler.start()
+    t0.record()
+    for _ in range(K):
+        step()
+    t1.record()
+    barrier()
+    if sampler:
+        sampler.stop()
+    ms_total = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
+    ms = float(ms_total) / K
+
+    # ---- the dominant kernel alone, CUDA events on its launching stream -------------------------
+    # N=1: the step IS one launch of the fused kernel (24 B/elem).  N>1: kernel (1) pseudo-gradient
+    # over the whole space (12 B/elem) is the largest HBM mover; time it on its own.
+    if world == 1:
+        kern_ms, kern_bytes, kern_name = ms, 24.0 * n, "outer_fused<W=1> (flat_kernel)"
+    else:
+        k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        k0.record()
+        for _ in range(K):
+            _lib.pseudo_grad(master, local, pg)
+        k1.record()
+        torch.cuda.synchronize()
+        kern_ms, kern_bytes, kern_name = k0.elapsed_time(k1) / K, 12.0 * n, "pseudo_grad (flat_kernel)"
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "of measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "of fallback (B200_PROFILING.md)"
+    achieved = kern_bytes / (kern_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            tj = json.load(open(tpath))
+            if world == 1 and tj.get("kernel") == "outer_fused_w1" and tj.get("elems"):
+                traffic = tj["dram_bytes_per_launch"] * (n / tj["elems"])
+        except Exception:  # noqa: BLE001
+            traffic = None
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": traffic, "kernel": kern_name, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": kern_bytes, "kernel_ms": kern_ms}
+
+    # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
+    hbm_bytes = (24.0 if world == 1 else 12.0 + 24.0 / world) * n
+    nvl_bytes = 0.0 if world == 1 else 8.0 * (world - 1) / world * n
+    step_roof = {"hbm_algorithmic_gbs": hbm_bytes / (ms * 1e-3) / 1e9,
+                 "nvlink_algorithmic_gbs_per_dir": nvl_bytes / (ms * 1e-3) / 1e9,
+                 "t_hbm_ms": hbm_bytes / (peak * 1e9) * 1e3, "t_nvlink_ms_at_900": nvl_bytes / 900e9 * 1e3}
+    bound_ms = max(step_roof["t_hbm_ms"], step_roof["t_nvlink_ms_at_900"])
+    step_roof["frac_of_overlapped_bound"] = bound_ms / ms
+
+    # ---- e2e: last-sync copy in pinned HOST memory, H2D + D2H inside the timed region ------------
+    e2e = None
+    if world == 1:
+        Ke = max(2, min(K, args.e2e_steps))
+        chunk = max(4, int(args.offload_chunk_mb * (1 << 20)) // 4 // 4 * 4)
+        octx = SyncContext(1, 0, bucket_elems=chunk, n_streams=3, device=dev)
+        master_host = torch.empty(n, dtype=torch.float32, pin_memory=True)
+        master_host.copy_(master)
+        staging = torch.empty(3 * chunk, device=dev)
+        for _ in range(2):
+            octx.outer_step_offloaded(master_host, staging, chunk, mom, local, **hyper)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        if sampler:
+            sampler.start()
+        e0.record()
+        for _ in range(Ke):
+            octx.outer_step_offloaded(master_host, staging, chunk, mom, local, **hyper)
+        e1.record()
+        barrier()
+        if sampler:
+            sampler.stop()
+        e2e = {"value": e0.elapsed_time(e1) / Ke, "unit": UNIT, "h2d_bytes_per_step": 4 * n,
+               "d2h_bytes_per_step": 4 * n, "steps": Ke,
+               "what": "nd_outer_step_offloaded: master copy in pinned host memory (the reference's layout), "
+                       "streamed H2D -> fused kernel -> D2H in %.0f MiB chunks over 3 streams" % args.offload_chunk_mb}
+        octx.close()
+        del master_host, staging
+    if sampler:
+        sampler.close()
+
+    # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------------------
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 3, 1, budget_s=args.cpu_budget_s)
+
+    if world > 1:
+        launches_per_step = 2 * ((n + ctx.bucket - 1) // ctx.bucket)   # K1 + K2 per bucket
+    else:
+        launches_per_step = 1
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": ms, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+            "ms_per_step": ms, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, n_real, len(shapes), world),
+            "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "clocks": sampler.summary() if sampler else None,
+            "gpu_launches": int(launches_per_step * K),
+            "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
+            "bucket_mb": args.bucket_mb if world > 1 else None,
+        }
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", choices=["native", "reference"], default="native")
+    ap.add_argument("--workload", choices=sorted(WORKLOADS), default="llama1b")
+    ap.add_argument("--bucket-mb", type=float, default=64.0)
+    ap.add_argument("--streams", type=int, default=2)
+    ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return native_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -207,7 +207,20 @@ int nd_outer_sync(nd_sync_ctx* ctx, float* local, float* master, float* mom_shar
                   int64_t n_padded, float lr, float mu, float dampening, float wd,
                   int nesterov, int first_step, nd_stream_t stream);
 
-/* Device milliseconds of the last nd_outer_sync on this rank (blocks until it
+/* The outer step with the last-sync copy resident in HOST memory, where the reference
+ * keeps it (diloco.py:25-32 offloads it, :47 copies it back per tensor, :54 offloads
+ * again).  World size 1.  The flat space is cut into chunks; chunk k rides side stream
+ * k % n_streams:  H2D(master chunk, pinned host -> staging slot)  ->  nd_outer_fused on
+ * the slot  ->  D2H(new master chunk), so the two PCIe directions and the kernel overlap.
+ * master_host: n floats of page-locked host memory (updated in place)
+ * staging:     device buffer of n_streams * chunk_elems floats
+ * Ordered on `stream` on return; nothing is synchronised. */
+int nd_outer_step_offloaded(nd_sync_ctx* ctx, float* master_host, float* staging, int64_t chunk_elems,
+                            float* mom, void* local, int local_dtype, int64_t n,
+                            float lr, float mu, float dampening, float wd,
+                            int nesterov, int first_step, nd_stream_t stream);
+
+/* Device milliseconds of the last nd_outer_sync / nd_outer_step_offloaded on this rank (blocks until it
  * has finished) -- what the reference's dead `avg_sync_time` (diloco.py:62-64)
  * promised. */
 int nd_sync_last_ms(nd_sync_ctx* ctx, float* ms_out);

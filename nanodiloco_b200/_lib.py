@@ -46,6 +46,8 @@ SIGNATURES = {
     "nd_sync_shard_elems": (_c_i64, [_c_p, _c_i64]),
     "nd_sync_bucket_elems": (_c_i64, [_c_p]),
     "nd_outer_sync": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_p, _c_i64, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p]),
+    "nd_outer_step_offloaded": (_c_i, [_c_p, _c_p, _c_p, _c_i64, _c_p, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f,
+                                       _c_i, _c_i, _c_p]),
     "nd_sync_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
 }
 

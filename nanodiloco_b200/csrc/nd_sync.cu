@@ -251,6 +251,44 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
     return ND_OK;
 }
 
+int nd_outer_step_offloaded(nd_sync_ctx* c, float* master_host, float* staging, int64_t chunk_elems, float* mom,
+                            void* local, int local_dtype, int64_t n, float lr, float mu, float dampening, float wd,
+                            int nesterov, int first_step, nd_stream_t stream_) {
+    if (!c) return set_error(ND_ESTATE, "nd_outer_step_offloaded: null context");
+    if (c->world != 1) return set_error(ND_ESTATE, "nd_outer_step_offloaded: world size must be 1");
+    if (n < 0 || chunk_elems < 4 || chunk_elems % 4 != 0)
+        return set_error(ND_EINVAL, "nd_outer_step_offloaded: chunk_elems must be a positive multiple of 4");
+    if (n && (!master_host || !staging || !mom || !local))
+        return set_error(ND_EINVAL, "nd_outer_step_offloaded: null pointer");
+    if (local_dtype != ND_F32 && local_dtype != ND_BF16)
+        return set_error(ND_EINVAL, "nd_outer_step_offloaded: unknown local_dtype");
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    const size_t lsz = local_dtype == ND_BF16 ? 2 : 4;
+    ND_CUDA(cudaEventRecord(c->t0, stream));
+    ND_CUDA(cudaEventRecord(c->fork, stream));
+    for (int i = 0; i < c->n_streams; ++i) ND_CUDA(cudaStreamWaitEvent(c->streams[i], c->fork, 0));
+    int64_t k = 0;
+    for (int64_t off = 0; off < n; off += chunk_elems, ++k) {
+        const int64_t len = (n - off < chunk_elems) ? (n - off) : chunk_elems;
+        const int slot = (int)(k % c->n_streams);
+        cudaStream_t s = c->streams[slot];  // stream order also protects the slot from reuse
+        float* m_dev = staging + (int64_t)slot * chunk_elems;
+        ND_CUDA(cudaMemcpyAsync(m_dev, master_host + off, (size_t)len * 4, cudaMemcpyHostToDevice, s));
+        void* locals[1] = {static_cast<char*>(local) + (size_t)off * lsz};
+        int rc = nd_outer_fused(m_dev, mom + off, locals, 1, local_dtype, len, lr, mu, dampening, wd, nesterov,
+                                first_step, nullptr, nullptr, reinterpret_cast<nd_stream_t>(s));
+        if (rc) return rc;
+        ND_CUDA(cudaMemcpyAsync(master_host + off, m_dev, (size_t)len * 4, cudaMemcpyDeviceToHost, s));
+    }
+    for (int i = 0; i < c->n_streams; ++i) {
+        ND_CUDA(cudaEventRecord(c->done[i], c->streams[i]));
+        ND_CUDA(cudaStreamWaitEvent(stream, c->done[i], 0));
+    }
+    ND_CUDA(cudaEventRecord(c->t1, stream));
+    c->timed = true;
+    return ND_OK;
+}
+
 int nd_sync_last_ms(nd_sync_ctx* c, float* ms_out) {
     if (!c || !ms_out) return set_error(ND_EINVAL, "nd_sync_last_ms: null argument");
     if (!c->timed) return set_error(ND_ESTATE, "nd_sync_last_ms: no nd_outer_sync has run");

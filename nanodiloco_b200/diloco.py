@@ -69,6 +69,8 @@ class Diloco:
         process_group=None,
         fused_inner: bool = True,
         max_grad_norm: float = 1.0,
+        offload_master: bool = False,
+        offload_chunk_mb: float = 64.0,
     ):
         # diloco.py:17-20
         self.model = model
@@ -118,10 +120,24 @@ class Diloco:
             dist.broadcast(self._local, src=dist.get_global_rank(process_group, 0) if process_group else 0,
                            group=process_group)
 
-        # diloco.py:25: theta_sync, kept in HBM
-        self._master = self._local.clone()
+        # diloco.py:25: theta_sync.  Kept in HBM by default; `offload_master=True` keeps it in
+        # page-locked host memory like the reference (diloco.py:27-32) and streams it through
+        # a small staging buffer during the outer step.
+        self.offload_master = offload_master
         self._first_outer = True
         self._scratch = _lib.scratch(dev)
+        if offload_master:
+            if W > 1:
+                raise NotImplementedError("offload_master is implemented for world size 1")
+            from .sync import SyncContext
+            self._master = torch.empty(n, dtype=torch.float32, pin_memory=True)
+            self._master.copy_(self._local)
+            self._off_chunk = max(4, int(offload_chunk_mb * (1 << 20)) // 4 // 4 * 4)
+            self._off_ctx = SyncContext(1, 0, bucket_elems=self._off_chunk, n_streams=max(3, n_streams),
+                                        device=dev)
+            self._staging = torch.empty(max(3, n_streams) * self._off_chunk, dtype=torch.float32, device=dev)
+        else:
+            self._master = self._local.clone()
 
         # ---- sharded sync context -------------------------------------------------------------
         self._ctx = None
@@ -185,7 +201,8 @@ class Diloco:
 
     @property
     def offloaded_last_sync_parameters(self) -> List[torch.Tensor]:
-        """theta_sync per tensor (diloco.py:25,54) -- views of the HBM-resident master copy."""
+        """theta_sync per tensor (diloco.py:25,54) -- views of the master copy (HBM-resident, or
+        host-resident with `offload_master=True`; then synchronise the stream before reading)."""
         return self.layout.views(self._master)
 
     def _get_offloaded_parameters(self):  # diloco.py:27-32, for callers that used it
@@ -203,7 +220,17 @@ class Diloco:
         t1 = torch.cuda.Event(enable_timing=True)
         t0.record(stream)
         first = self._first_outer
-        if self._ctx is None:
+        if self.offload_master:
+            if len(self._outer_ranges) != 1:
+                raise NotImplementedError("offload_master supports a single outer param group")
+            g = self._outer_ranges[0][0]
+            self._check_outer_group(g)
+            self._off_ctx.outer_step_offloaded(self._master, self._staging, self._off_chunk, self._mom,
+                                               self._local, lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                               dampening=float(g["dampening"]),
+                                               weight_decay=float(g["weight_decay"]),
+                                               nesterov=bool(g["nesterov"]), first_step=first)
+        elif self._ctx is None:
             for g, s, e in self._outer_ranges:
                 self._check_outer_group(g)
                 _lib.outer_fused(self._master[s:e], self._mom[s:e], [self._local[s:e]],

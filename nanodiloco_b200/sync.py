@@ -68,6 +68,17 @@ class SyncContext:
                                              int(nesterov), int(first_step), _lib._stream(stream)),
                    "nd_outer_sync")
 
+    def outer_step_offloaded(self, master_host, staging, chunk_elems, mom, local, *, lr, momentum,
+                             dampening=0.0, weight_decay=0.0, nesterov=True, first_step=False, stream=None) -> None:
+        """nd_outer_step_offloaded: last-sync copy in pinned host memory (reference semantics)."""
+        if master_host.is_cuda or not master_host.is_pinned():
+            raise _lib.NDError("master_host must be page-locked host memory")
+        _lib._require_cuda(staging, mom, local)
+        _lib.check(_lib.load().nd_outer_step_offloaded(
+            self._h, master_host.data_ptr(), _lib._ptr(staging), int(chunk_elems), _lib._ptr(mom), _lib._ptr(local),
+            _lib._dtype_code(local), local.numel(), lr, momentum, dampening, weight_decay, int(nesterov),
+            int(first_step), _lib._stream(stream)), "nd_outer_step_offloaded")
+
     def last_ms(self) -> float:
         ms = ctypes.c_float()
         _lib.check(_lib.load().nd_sync_last_ms(self._h, ctypes.byref(ms)), "nd_sync_last_ms")

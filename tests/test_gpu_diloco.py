@@ -105,3 +105,28 @@ def test_training_loop_with_autograd():
     assert losses[-1] < 0.5 * losses[0]
     for p, q in zip(model.parameters(), d.offloaded_last_sync_parameters):
         assert torch.equal(p.data, q)                                 # just synced
+
+
+def test_outer_step_offloaded_master_matches_resident(golden_dir):
+    """Reference semantics: the last-sync copy lives on the HOST (diloco.py:25-32,47,54).  Same bits
+    as the HBM-resident path and as the reference's golden vectors, with chunks smaller than,
+    equal to and larger than the parameter space."""
+    z = np.load(os.path.join(golden_dir, "outer_w1.npz"))
+    for chunk_mb in (0.001, 0.01, 64.0):
+        model, inner, outer, d = _make(z, warmup_steps=2, total_steps=100, offload_master=True,
+                                       offload_chunk_mb=chunk_mb)
+        params = list(model.parameters())
+        for r in range(3):
+            loc, off = z[f"local_r{r}_w0"], 0
+            with torch.no_grad():
+                for p in params:
+                    p.copy_(torch.from_numpy(loc[off:off + p.numel()]).reshape(p.shape))
+                    off += p.numel()
+            d.outer_step()
+            torch.cuda.synchronize()
+            assert np.array_equal(host(_flat(params)), z[f"params_r{r}"])
+            snap = d.offloaded_last_sync_parameters
+            assert all(not t.is_cuda for t in snap)                    # on the host, like the reference's
+            assert np.array_equal(_flat(snap).numpy(), z[f"params_r{r}"])
+            mom = _flat([outer.state[p]["momentum_buffer"] for p in params])
+            assert np.array_equal(host(mom), z[f"mom_r{r}"])
