@@ -13,7 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libnanodiloco_b200.so")
 SOURCES = ["nd_kernels.cu", "nd_sync.cu"]
-HEADERS = ["nd_common.cuh", "nd_error.h", os.path.join("..", "..", "include", "nanodiloco_b200.h")]
+HEADERS = ["nd_common.cuh", "nd_error.h", "nd_tma.cuh", os.path.join("..", "..", "include", "nanodiloco_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -22,6 +22,7 @@
 
 #include "nd_common.cuh"
 #include "nd_error.h"
+#include "nd_tma.cuh"
 
 namespace nd {
 
@@ -294,6 +295,156 @@ struct HasPrologue<Op, decltype(std::declval<Op&>().prologue(), void())> {
     static constexpr bool value = true;
 };
 
+
+// ===========================================================================
+// TileOps: the same arithmetic on shared-memory tiles for the TMA-staged driver (nd_tma.cuh).
+// Each wraps the register-path Op above (pointers, hyper-parameters, scalar tail).
+// ===========================================================================
+
+__device__ __forceinline__ float4 lds4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ void sts4(float* p, const float4& v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ float4 lds_bf16x4(const float* buf, int i) {
+    uint2 raw = *reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(buf) + i);
+    float2 a = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&raw.x));
+    float2 b = __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&raw.y));
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void sts_bf16x4(float* buf, int i, const float4& v) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 raw;
+    raw.x = *reinterpret_cast<unsigned*>(&lo);
+    raw.y = *reinterpret_cast<unsigned*>(&hi);
+    *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(buf) + i) = raw;
+}
+
+// buffers: 0 = master -> new params, 1 = momentum, 2.. = the W local copies (buffer 2 is reused
+// for the bf16 image of the new params when the working copy is bf16)
+template <int W, bool BF16, bool SUM>
+struct FusedTileOp {
+    static_assert(W >= 1, "compile-time worker count");
+    static constexpr int kBufs = 2 + W;
+    static constexpr bool kHasSum = SUM;
+    static constexpr int kEsz = BF16 ? 2 : 4;
+    static constexpr int kGran = 16 / kEsz;
+    OuterFusedOp<W, BF16, SUM> o;
+    __device__ __forceinline__ void prologue() { o.acc = 0.0f; }
+    __device__ __forceinline__ float acc() const { return o.acc; }
+    __device__ __forceinline__ uint32_t load_bytes(int len) const {
+        return (uint32_t)len * ((o.h.first_step ? 4u : 8u) + (uint32_t)(W * kEsz));
+    }
+    template <int TILE>
+    __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
+        tma::bulk_load(st.buf(0), o.master + off, (uint32_t)len * 4, bar);
+        if (!o.h.first_step) tma::bulk_load(st.buf(1), o.mom + off, (uint32_t)len * 4, bar);
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+            tma::bulk_load(st.buf(2 + k), static_cast<const char*>(o.locals.p[k]) + off * kEsz, (uint32_t)len * kEsz, bar);
+    }
+    template <int TILE>
+    __device__ __forceinline__ void compute(const tma::Stage<TILE>& st, int len, int tid, int nthreads) {
+        for (int i = tid * 4; i < len; i += nthreads * 4) {
+            float4 p = lds4(st.buf(0) + i);
+            float4 b = o.h.first_step ? make_float4(0.f, 0.f, 0.f, 0.f) : lds4(st.buf(1) + i);
+            float4 s;
+#pragma unroll
+            for (int k = 0; k < W; ++k) {
+                float4 l = BF16 ? lds_bf16x4(st.buf(2 + k), i) : lds4(st.buf(2 + k) + i);
+                float4 d = make_float4(__fsub_rn(p.x, l.x), __fsub_rn(p.y, l.y), __fsub_rn(p.z, l.z), __fsub_rn(p.w, l.w));
+                if (k == 0) s = d;
+                else s = make_float4(__fadd_rn(s.x, d.x), __fadd_rn(s.y, d.y), __fadd_rn(s.z, d.z), __fadd_rn(s.w, d.w));
+            }
+            o.one(p.x, b.x, s.x); o.one(p.y, b.y, s.y); o.one(p.z, b.z, s.z); o.one(p.w, b.w, s.w);
+            sts4(st.buf(0) + i, p);
+            sts4(st.buf(1) + i, b);
+            if (BF16) sts_bf16x4(st.buf(2), i, p);
+        }
+    }
+    template <int TILE>
+    __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
+        tma::bulk_store(o.master + off, st.buf(0), (uint32_t)len * 4);
+        tma::bulk_store(o.mom + off, st.buf(1), (uint32_t)len * 4);
+#pragma unroll
+        for (int k = 0; k < W; ++k)
+            tma::bulk_store(static_cast<char*>(o.locals.p[k]) + off * kEsz, st.buf(BF16 ? 2 : 0), (uint32_t)len * kEsz);
+    }
+    __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
+};
+
+// buffers: 0 = master shard, 1 = momentum shard, 2 = reduced pseudo-gradient (reused for the bf16 copy-back)
+template <bool BF16, bool SUM>
+struct ShardTileOp {
+    static constexpr int kBufs = 3;
+    static constexpr bool kHasSum = SUM;
+    static constexpr int kEsz = BF16 ? 2 : 4;
+    static constexpr int kGran = 16 / kEsz;
+    OuterShardOp<BF16, SUM> o;
+    __device__ __forceinline__ void prologue() { o.acc = 0.0f; }
+    __device__ __forceinline__ float acc() const { return o.acc; }
+    __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * (o.h.first_step ? 8u : 12u); }
+    template <int TILE>
+    __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
+        tma::bulk_load(st.buf(0), o.master + off, (uint32_t)len * 4, bar);
+        if (!o.h.first_step) tma::bulk_load(st.buf(1), o.mom + off, (uint32_t)len * 4, bar);
+        tma::bulk_load(st.buf(2), o.pg_sum + off, (uint32_t)len * 4, bar);
+    }
+    template <int TILE>
+    __device__ __forceinline__ void compute(const tma::Stage<TILE>& st, int len, int tid, int nthreads) {
+        for (int i = tid * 4; i < len; i += nthreads * 4) {
+            float4 p = lds4(st.buf(0) + i);
+            float4 b = o.h.first_step ? make_float4(0.f, 0.f, 0.f, 0.f) : lds4(st.buf(1) + i);
+            float4 g = lds4(st.buf(2) + i);
+            o.one(p.x, b.x, g.x); o.one(p.y, b.y, g.y); o.one(p.z, b.z, g.z); o.one(p.w, b.w, g.w);
+            sts4(st.buf(0) + i, p);
+            sts4(st.buf(1) + i, b);
+            if (BF16) sts_bf16x4(st.buf(2), i, p);
+        }
+    }
+    template <int TILE>
+    __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
+        tma::bulk_store(o.master + off, st.buf(0), (uint32_t)len * 4);
+        tma::bulk_store(o.mom + off, st.buf(1), (uint32_t)len * 4);
+        if (o.local_out)
+            tma::bulk_store(static_cast<char*>(o.local_out) + off * kEsz, st.buf(BF16 ? 2 : 0), (uint32_t)len * kEsz);
+    }
+    __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
+};
+
+// buffers: 0 = p, 1 = g (zeroed in place when zero_grad), 2 = exp_avg, 3 = exp_avg_sq
+struct AdamTileOp {
+    static constexpr int kBufs = 4;
+    static constexpr bool kHasSum = false;
+    static constexpr int kGran = 4;
+    AdamWOp o;
+    __device__ __forceinline__ void prologue() { o.prologue(); }
+    __device__ __forceinline__ float acc() const { return 0.0f; }
+    __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * 16u; }
+    template <int TILE>
+    __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
+        tma::bulk_load(st.buf(0), o.p + off, (uint32_t)len * 4, bar);
+        tma::bulk_load(st.buf(1), o.g + off, (uint32_t)len * 4, bar);
+        tma::bulk_load(st.buf(2), o.m + off, (uint32_t)len * 4, bar);
+        tma::bulk_load(st.buf(3), o.v + off, (uint32_t)len * 4, bar);
+    }
+    template <int TILE>
+    __device__ __forceinline__ void compute(const tma::Stage<TILE>& st, int len, int tid, int nthreads) {
+        for (int i = tid * 4; i < len; i += nthreads * 4) {
+            float4 p = lds4(st.buf(0) + i), g = lds4(st.buf(1) + i), m = lds4(st.buf(2) + i), v = lds4(st.buf(3) + i);
+            o.one(p.x, g.x, m.x, v.x); o.one(p.y, g.y, m.y, v.y);
+            o.one(p.z, g.z, m.z, v.z); o.one(p.w, g.w, m.w, v.w);
+            sts4(st.buf(0) + i, p); sts4(st.buf(2) + i, m); sts4(st.buf(3) + i, v);
+            if (o.h.zero_grad) sts4(st.buf(1) + i, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
+    }
+    template <int TILE>
+    __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
+        tma::bulk_store(o.p + off, st.buf(0), (uint32_t)len * 4);
+        tma::bulk_store(o.m + off, st.buf(2), (uint32_t)len * 4);
+        tma::bulk_store(o.v + off, st.buf(3), (uint32_t)len * 4);
+        if (o.h.zero_grad) tma::bulk_store(o.g + off, st.buf(1), (uint32_t)len * 4);
+    }
+    __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
+};
+
 // ===========================================================================
 // Drivers
 // ===========================================================================
@@ -412,6 +563,32 @@ static int launch_table(const Op& op, const nd_tensor_desc* tab, int T, int64_t 
     return check_launch("table_kernel");
 }
 
+
+// TMA-staged launch: TILE fp32 slots per buffer, STAGES stages, THREADS threads, MINB CTAs per SM.
+template <int TILE, int STAGES, int THREADS, int MINB, class TileOp>
+static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_out, cudaStream_t s) {
+    if (n == 0 && !TileOp::kHasSum) return ND_OK;
+    auto kernel = tma::tile_kernel<TILE, STAGES, THREADS, MINB, TileOp>;
+    constexpr size_t smem = (size_t)STAGES * TileOp::kBufs * TILE * sizeof(float);
+    static_assert(smem <= 227 * 1024, "stage set exceeds the 227 KB of shared memory a CTA can have");
+    static bool configured[64] = {false};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (!configured[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error(ND_ECUDA, "cudaFuncSetAttribute(smem=%zu): %s", smem, cudaGetErrorString(e));
+        configured[dev] = true;
+    }
+    const int64_t ntiles = ((n & ~(int64_t)(TileOp::kGran - 1)) + TILE - 1) / TILE;
+    int64_t full = (int64_t)sm_count() * MINB;
+    int64_t g = ntiles < full ? (ntiles > 0 ? ntiles : 1) : full;
+    if (g > kMaxPartials) g = kMaxPartials;
+    kernel<<<(int)g, THREADS, smem, s>>>(op, n, static_cast<Scratch*>(scratch), sum_out);
+    return check_launch("tile_kernel");
+}
+
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
 static OuterHyper make_outer_hyper(float lr, float mu, float dampening, float wd, int nesterov, int first) {
     OuterHyper h;
     h.neg_lr = -lr; h.mu = mu; h.one_minus_damp = 1.0f - dampening; h.wd = wd;
@@ -438,22 +615,42 @@ static AdamHyper make_adam_hyper(double lr, double b1, double b2, double eps, do
     return h;
 }
 
-// tuning knobs: groups in flight per thread / resident CTAs per SM
-constexpr int U_PG = 2, B_PG = 4;
-constexpr int U_SHARD = 2, B_SHARD = 3;
+// Tuning knobs (tools/tune.cu sweeps them on the box; profiles/ holds the sweep).
+// Register-staged path: U groups in flight per thread / B resident CTAs per SM.  Lower occupancy
+// with fewer, fatter threads streams better here than 2048 threads/SM.
+constexpr int U_PG = 1, B_PG = 4;
+constexpr int U_SHARD = 1, B_SHARD = 2;
 constexpr int U_SUMSQ = 4, B_SUMSQ = 4;
-constexpr int U_ADAM = 1, B_ADAM = 3;
+constexpr int U_ADAM = 1, B_ADAM = 2;
+// TMA-staged path: fp32 slots per buffer per stage / stages / threads / CTAs per SM.
+#define ND_TILE_FUSED1 4096, 2, 512, 2
+#define ND_TILE_FUSED2 4096, 2, 512, 1
+#define ND_TILE_FUSED4 1024, 3, 256, 3
+#define ND_TILE_FUSED8 1024, 3, 256, 1
+#define ND_TILE_SHARD 4096, 2, 512, 2
+#define ND_TILE_ADAM 2048, 2, 512, 2
 
 template <int W, bool BF16, bool SUM>
 static int launch_fused(float* master, float* mom, void* const* locals, int w_rt, int64_t n, const OuterHyper& h,
                         float* sumsq_out, void* scratch, cudaStream_t s) {
     OuterFusedOp<W, BF16, SUM> op;
     op.master = master; op.mom = mom; op.w_rt = w_rt; op.world = (float)w_rt; op.h = h; op.acc = 0.f;
-    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k < w_rt ? locals[k] : nullptr;
-    // registers: (2 + W) float4 per group; keep >= 1536 threads/SM while it fits
-    if constexpr (W == 1) return launch_flat<2, 3>(op, n, scratch, sumsq_out, s);
-    else if constexpr (W == 2) return launch_flat<2, 2>(op, n, scratch, sumsq_out, s);
-    else if constexpr (W > 0 && W <= 4) return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
+    bool al = aligned16(master) && aligned16(mom);
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) {
+        op.locals.p[k] = k < w_rt ? locals[k] : nullptr;
+        al = al && aligned16(op.locals.p[k]);
+    }
+    if constexpr (W > 0) {
+        if (al) {  // TMA-staged path: every bulk copy needs 16-byte aligned addresses
+            FusedTileOp<W, BF16, SUM> t{op};
+            if constexpr (W == 1) return launch_tile<ND_TILE_FUSED1>(t, n, scratch, sumsq_out, s);
+            else if constexpr (W == 2) return launch_tile<ND_TILE_FUSED2>(t, n, scratch, sumsq_out, s);
+            else if constexpr (W <= 4) return launch_tile<ND_TILE_FUSED4>(t, n, scratch, sumsq_out, s);
+            else return launch_tile<ND_TILE_FUSED8>(t, n, scratch, sumsq_out, s);
+        }
+    }
+    // register-staged path: unaligned buffers (scalar accesses) and run-time worker counts
+    if constexpr (W == 1) return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
     else return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
 }
 
@@ -534,6 +731,10 @@ int nd_outer_nesterov(float* master, float* mom, const float* pg_sum, void* loca
         OuterShardOp<BF, SM> op;                                                             \
         op.master = master; op.mom = mom; op.pg_sum = pg_sum; op.local_out = local_out;      \
         op.world = world; op.h = h; op.acc = 0.f;                                            \
+        if (aligned16(master) && aligned16(mom) && aligned16(pg_sum) && aligned16(local_out)) { \
+            ShardTileOp<BF, SM> t{op};                                                       \
+            return launch_tile<ND_TILE_SHARD>(t, n, scratch, sumsq_out, s);                  \
+        }                                                                                    \
         return launch_flat<U_SHARD, B_SHARD>(op, n, scratch, sumsq_out, s);                  \
     } while (0)
     if (local_dtype == ND_BF16) { if (sumsq_out) ND_SHARD(true, true); else ND_SHARD(true, false); }
@@ -610,6 +811,10 @@ int nd_adamw(float* p, float* g, float* m, float* v, int64_t n, double lr, doubl
     AdamWOp op;
     op.p = p; op.g = g; op.m = m; op.v = v; op.sumsq = sumsq_dev; op.coef = 1.f;
     op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+    if (aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v)) {
+        AdamTileOp t{op};
+        return launch_tile<ND_TILE_ADAM>(t, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
+    }
     return launch_flat<U_ADAM, B_ADAM>(op, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
 }
 

@@ -20,127 +20,6 @@
         }                                                                             \
     } while (0)
 
-// ---------------------------------------------------------------------------------------------
-// TMA-bulk variant of the fused W=1 outer kernel.
-// Each CTA owns tiles t = blockIdx.x, blockIdx.x + gridDim.x, ...; a tile is TILE floats of each
-// of the three arrays.  STAGES smem stages; thread 0 issues cp.async.bulk loads (mbarrier
-// complete_tx) and bulk stores; all threads compute in place in shared memory.
-// ---------------------------------------------------------------------------------------------
-namespace tma {
-
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(uint64_t* b, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(b)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t* b, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(b)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint64_t* b, uint32_t parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(b)), "r"(parity)
-        : "memory");
-}
-__device__ __forceinline__ void bulk_load(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst_smem)),
-                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_store(void* dst_gmem, const void* src_smem, uint32_t bytes) {
-    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst_gmem), "r"(smem_u32(src_smem)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void bulk_wait_read() {
-    asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
-}
-__device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-template <int TILE, int STAGES, int THREADS>
-__global__ void __launch_bounds__(THREADS) fused_w1_tma(float* __restrict__ master, float* __restrict__ mom,
-                                                        float* __restrict__ local, int64_t n, nd::OuterHyper h) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    float* sm = reinterpret_cast<float*>(smem_raw);  // [STAGES][3][TILE]
-    __shared__ uint64_t full[STAGES];
-    const int64_t ntiles = (n + TILE - 1) / TILE;
-    const int tid = threadIdx.x;
-    if (tid == 0) {
-        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    __syncthreads();
-
-    auto issue_load = [&](int64_t tile, int s) {
-        const int64_t off = tile * TILE;
-        const uint32_t len = (uint32_t)((n - off < TILE ? n - off : TILE) * 4);
-        float* base = sm + (size_t)s * 3 * TILE;
-        mbar_expect_tx(&full[s], 3 * len);
-        bulk_load(base, master + off, len, &full[s]);
-        bulk_load(base + TILE, mom + off, len, &full[s]);
-        bulk_load(base + 2 * TILE, local + off, len, &full[s]);
-    };
-
-    // prologue: fill STAGES-1 stages
-    if (tid == 0) {
-        for (int k = 0; k < STAGES - 1; ++k) {
-            int64_t t = blockIdx.x + (int64_t)k * gridDim.x;
-            if (t < ntiles) issue_load(t, k);
-        }
-    }
-    int it = 0;
-    for (int64_t tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++it) {
-        const int s = it % STAGES;
-        const uint32_t parity = (it / STAGES) & 1;
-        // refill: the stage used STAGES-1 iterations ahead is the one consumed last iteration
-        if (tid == 0) {
-            int64_t tnext = tile + (int64_t)(STAGES - 1) * gridDim.x;
-            if (tnext < ntiles) {
-                bulk_wait_read<0>();  // its stores have finished reading shared memory
-                issue_load(tnext, (it + STAGES - 1) % STAGES);
-            }
-        }
-        mbar_wait(&full[s], parity);
-        const int64_t off = tile * TILE;
-        const int len = (int)(n - off < TILE ? n - off : TILE);
-        float* pm = sm + (size_t)s * 3 * TILE;
-        float* pb = pm + TILE;
-        float* pl = pm + 2 * TILE;
-        for (int i = tid * 4; i < len; i += THREADS * 4) {
-            float4 p = *reinterpret_cast<float4*>(pm + i);
-            float4 b = *reinterpret_cast<float4*>(pb + i);
-            float4 l = *reinterpret_cast<float4*>(pl + i);
-            nd::outer_update(__fsub_rn(p.x, l.x), p.x, b.x, h);
-            nd::outer_update(__fsub_rn(p.y, l.y), p.y, b.y, h);
-            nd::outer_update(__fsub_rn(p.z, l.z), p.z, b.z, h);
-            nd::outer_update(__fsub_rn(p.w, l.w), p.w, b.w, h);
-            *reinterpret_cast<float4*>(pm + i) = p;
-            *reinterpret_cast<float4*>(pb + i) = b;
-        }
-        fence_async();
-        __syncthreads();
-        if (tid == 0) {
-            const uint32_t bytes = (uint32_t)len * 4;
-            bulk_store(master + off, pm, bytes);
-            bulk_store(local + off, pm, bytes);
-            bulk_store(mom + off, pb, bytes);
-            bulk_commit();
-        }
-    }
-    if (tid == 0) bulk_wait_read<0>();
-    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
-}
-
-}  // namespace tma
-
 __global__ void copy_kernel(const float4* __restrict__ a, float4* __restrict__ b, int64_t nvec) {
     int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -219,17 +98,42 @@ static void sumsq_variant(float* g, int64_t n, int sms, void* scratch, float* ou
     report(name, ms, 4.0 * n);
 }
 
-template <int TILE, int STAGES, int THREADS>
-static void tma_variant(float* master, float* mom, float* local, int64_t n, int sms, int ctas_per_sm) {
-    auto k = tma::fused_w1_tma<TILE, STAGES, THREADS>;
-    size_t smem = (size_t)STAGES * 3 * TILE * 4;
-    CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    nd::OuterHyper h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
+template <int TILE, int STAGES, int THREADS, int MINB>
+static void tma_fused(float* master, float* mom, float* local, int64_t n, int sms) {
+    nd::OuterFusedOp<1, false, false> op;
+    op.master = master; op.mom = mom; op.w_rt = 1; op.world = 1.f; op.acc = 0.f;
+    op.h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k == 0 ? local : nullptr;
+    nd::FusedTileOp<1, false, false> t{op};
     char name[96];
-    snprintf(name, sizeof name, "fused_w1 TMA tile=%dKB st=%d thr=%d cta/sm=%d", TILE * 4 / 1024, STAGES, THREADS,
-             ctas_per_sm);
-    float ms = time_ms([&] { k<<<sms * ctas_per_sm, THREADS, smem>>>(master, mom, local, n, h); });
+    snprintf(name, sizeof name, "fused_w1 TMA tile=%dKB st=%d thr=%d cta/sm=%d", TILE * 4 / 1024, STAGES, THREADS, MINB);
+    float ms = time_ms([&] { nd::launch_tile<TILE, STAGES, THREADS, MINB>(t, n, nullptr, nullptr, 0); });
     report(name, ms, 24.0 * n);
+}
+
+template <int TILE, int STAGES, int THREADS, int MINB>
+static void tma_adam(float* p, float* g, float* m, float* v, int64_t n, int sms) {
+    nd::AdamWOp op;
+    op.p = p; op.g = g; op.m = m; op.v = v; op.sumsq = nullptr; op.coef = 1.f;
+    op.h = nd::make_adam_hyper(4e-4, 0.9, 0.999, 1e-8, 1e-2, 10, 1.0f, 1);
+    nd::AdamTileOp t{op};
+    char name[96];
+    snprintf(name, sizeof name, "adamw(+zero_grad) TMA tile=%dKB st=%d thr=%d cta/sm=%d", TILE * 4 / 1024, STAGES, THREADS, MINB);
+    float ms = time_ms([&] { nd::launch_tile<TILE, STAGES, THREADS, MINB>(t, n, nullptr, nullptr, 0); });
+    report(name, ms, 32.0 * n);
+}
+
+template <int W, int TILE, int STAGES, int THREADS, int MINB>
+static void tma_fused_w(float* master, float* mom, float** locals, int64_t n, int sms) {
+    nd::OuterFusedOp<W, false, false> op;
+    op.master = master; op.mom = mom; op.w_rt = W; op.world = (float)W; op.acc = 0.f;
+    op.h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k < W ? locals[k] : nullptr;
+    nd::FusedTileOp<W, false, false> t{op};
+    char name[96];
+    snprintf(name, sizeof name, "fused W=%d TMA tile=%dKB st=%d thr=%d cta/sm=%d", W, TILE * 4 / 1024, STAGES, THREADS, MINB);
+    float ms = time_ms([&] { nd::launch_tile<TILE, STAGES, THREADS, MINB>(t, n, nullptr, nullptr, 0); });
+    report(name, ms, (16.0 + 8.0 * W) * n);
 }
 
 int main(int argc, char** argv) {
@@ -248,36 +152,6 @@ int main(int argc, char** argv) {
     report("cudaMemcpyAsync D2D (8 B/elem)", time_ms([&] { CK(cudaMemcpyAsync(b, a, n * 4, cudaMemcpyDeviceToDevice)); }), 8.0 * n);
     report("copy_kernel float4 x2 (8 B/elem)", time_ms([&] { copy_kernel<<<sms * 4, 512>>>((float4*)a, (float4*)b, n / 4); }), 8.0 * n);
 
-    // correctness of the TMA variant against the LDG kernel (small n, non-trivial values)
-    {
-        int64_t m = 1000003 / 4 * 4;
-        std::vector<float> hm(m), hl(m), hb(m);
-        for (int64_t i = 0; i < m; ++i) { hm[i] = 0.02f * sinf(i * 0.37f); hl[i] = hm[i] + 1e-3f * cosf(i * 0.11f); hb[i] = 1e-3f * sinf(i * 0.05f); }
-        float *x[6];
-        for (auto& p : x) CK(cudaMalloc(&p, m * 4));
-        for (int r = 0; r < 2; ++r) {
-            CK(cudaMemcpy(x[3 * r], hm.data(), m * 4, cudaMemcpyHostToDevice));
-            CK(cudaMemcpy(x[3 * r + 1], hb.data(), m * 4, cudaMemcpyHostToDevice));
-            CK(cudaMemcpy(x[3 * r + 2], hl.data(), m * 4, cudaMemcpyHostToDevice));
-        }
-        nd::OuterHyper h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
-        void* locals[1] = {x[2]};
-        nd_outer_fused(x[0], x[1], locals, 1, ND_F32, m, 0.7f, 0.9f, 0.f, 0.f, 1, 0, nullptr, nullptr, nullptr);
-        auto k = tma::fused_w1_tma<2048, 4, 256>;
-        CK(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 * 3 * 2048 * 4));
-        k<<<sms * 2, 256, 4 * 3 * 2048 * 4>>>(x[3], x[4], x[5], m, h);
-        CK(cudaDeviceSynchronize());
-        std::vector<float> r0(m), r1(m);
-        bool ok = true;
-        for (int j = 0; j < 3; ++j) {
-            CK(cudaMemcpy(r0.data(), x[j], m * 4, cudaMemcpyDeviceToHost));
-            CK(cudaMemcpy(r1.data(), x[3 + j], m * 4, cudaMemcpyDeviceToHost));
-            ok &= memcmp(r0.data(), r1.data(), m * 4) == 0;
-        }
-        printf("TMA variant bit-identical to LDG kernel: %s\n", ok ? "yes" : "NO");
-        for (auto& p : x) CK(cudaFree(p));
-    }
-
     fused_variant<1, 4>(a, b, c, n, sms);
     fused_variant<2, 4>(a, b, c, n, sms);
     fused_variant<1, 3>(a, b, c, n, sms);
@@ -290,14 +164,19 @@ int main(int argc, char** argv) {
     fused_variant<4, 1>(a, b, c, n, sms);
     fused_variant<8, 1>(a, b, c, n, sms);
 
-    tma_variant<2048, 4, 256>(a, b, c, n, sms, 2);
-    tma_variant<2048, 3, 256>(a, b, c, n, sms, 3);
-    tma_variant<4096, 4, 256>(a, b, c, n, sms, 1);
-    tma_variant<4096, 2, 512>(a, b, c, n, sms, 2);
-    tma_variant<1024, 4, 256>(a, b, c, n, sms, 4);
-    tma_variant<1024, 6, 128>(a, b, c, n, sms, 3);
-    tma_variant<2048, 8, 256>(a, b, c, n, sms, 1);
-
+    tma_fused<4096, 2, 512, 2>(a, b, c, n, sms);
+    tma_fused<4096, 2, 256, 2>(a, b, c, n, sms);
+    tma_fused<4096, 3, 512, 1>(a, b, c, n, sms);
+    tma_fused<4096, 4, 512, 1>(a, b, c, n, sms);
+    tma_fused<8192, 2, 512, 1>(a, b, c, n, sms);
+    tma_fused<2048, 3, 256, 3>(a, b, c, n, sms);
+    tma_fused<2048, 2, 256, 4>(a, b, c, n, sms);
+    tma_fused<2048, 4, 256, 2>(a, b, c, n, sms);
+    tma_fused<2048, 2, 128, 4>(a, b, c, n, sms);
+    tma_fused<1024, 4, 128, 4>(a, b, c, n, sms);
+    tma_fused<1024, 3, 128, 6>(a, b, c, n, sms);
+    tma_fused<1024, 2, 128, 8>(a, b, c, n, sms);
+    tma_fused<512, 4, 128, 8>(a, b, c, n, sms);
     pg_variant<1, 4>(a, c, d, n, sms);
     pg_variant<2, 4>(a, c, d, n, sms);
     pg_variant<4, 2>(a, c, d, n, sms);
@@ -315,5 +194,27 @@ int main(int argc, char** argv) {
     adam_variant<2, 2>(a, d, b, c, n, sms);
     adam_variant<2, 1>(a, d, b, c, n, sms);
     adam_variant<4, 1>(a, d, b, c, n, sms);
+    adam_variant<1, 1>(a, d, b, c, n, sms);
+    tma_adam<2048, 3, 256, 2>(a, d, b, c, n, sms);
+    tma_adam<2048, 2, 256, 3>(a, d, b, c, n, sms);
+    tma_adam<2048, 2, 512, 2>(a, d, b, c, n, sms);
+    tma_adam<4096, 2, 512, 1>(a, d, b, c, n, sms);
+    tma_adam<4096, 3, 512, 1>(a, d, b, c, n, sms);
+    tma_adam<1024, 3, 128, 4>(a, d, b, c, n, sms);
+    tma_adam<1024, 2, 256, 6>(a, d, b, c, n, sms);
+    tma_adam<1024, 4, 256, 3>(a, d, b, c, n, sms);
+    // several worker copies emulated on one GPU (each of n/4 elements so that everything fits)
+    {
+        int64_t m = n / 4 / 4 * 4;
+        float* loc[8];
+        for (int k = 0; k < 8; ++k) { CK(cudaMalloc(&loc[k], m * 4)); CK(cudaMemset(loc[k], 0, m * 4)); }
+        tma_fused_w<2, 2048, 3, 256, 2>(a, b, loc, m, sms);
+        tma_fused_w<2, 4096, 2, 512, 1>(a, b, loc, m, sms);
+        tma_fused_w<4, 2048, 2, 256, 2>(a, b, loc, m, sms);
+        tma_fused_w<4, 1024, 3, 256, 3>(a, b, loc, m, sms);
+        tma_fused_w<8, 2048, 2, 256, 1>(a, b, loc, m, sms);
+        tma_fused_w<8, 1024, 2, 256, 2>(a, b, loc, m, sms);
+        tma_fused_w<8, 1024, 3, 256, 1>(a, b, loc, m, sms);
+    }
     return 0;
 }
