@@ -252,18 +252,36 @@ def native_arm(args):
     n = layout.total
     K, Wm = args.steps, max(3, args.warmup)
 
+    from nanodiloco_b200.sync import PeerContext
+    mode = "none" if world == 1 else args.sync
     g = torch.Generator(device=dev).manual_seed(0)
-    master = torch.empty(n, device=dev).normal_(0, 0.02, generator=g)
+    master = torch.empty(n, device=dev).normal_(0, 0.02, generator=g)      # same on every rank (seed 0)
     gl = torch.Generator(device=dev).manual_seed(100 + rank)
-    local = master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)
-    ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
-                      device=dev)
-    mom = torch.zeros(ctx.shard_elems(n), device=dev)
-    pg = torch.empty(n, device=dev) if world > 1 else None
     hyper = dict(lr=OUTER_LR, momentum=OUTER_MU, dampening=0.0, weight_decay=0.0, nesterov=True)
+    ctx = pctx = None
+    if mode == "p2p":
+        # one fused kernel per GPU over NVLink peer memory; master and momentum sharded 1/W
+        pctx = PeerContext(world, rank, n, group=None, device=dev)
+        local = pctx.local()[:n]
+        local.copy_(master)
+        local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))
+        lo, hi = pctx.shard_range()
+        master = master[lo:hi].clone()
+        mom = torch.zeros(hi - lo, device=dev)
+        pg = None
+        torch.cuda.empty_cache()
 
-    def step(first=False):
-        ctx.outer_sync(local, master, mom, pg, first_step=first, **hyper)
+        def step(first=False):
+            pctx.outer_sync(master, mom, first_step=first, **hyper)
+    else:
+        local = master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)
+        ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
+                          device=dev)
+        mom = torch.zeros(ctx.shard_elems(n), device=dev)
+        pg = torch.empty(n, device=dev) if world > 1 else None
+
+        def step(first=False):
+            ctx.outer_sync(local, master, mom, pg, first_step=first, **hyper)
 
     def barrier():
         if world > 1:
@@ -297,7 +315,13 @@ def native_arm(args):
     # N=1: the step IS one launch of the fused kernel (24 B/elem).  N>1: kernel (1) pseudo-gradient
     # over the whole space (12 B/elem) is the largest HBM mover; time it on its own.
     if world == 1:
-        kern_ms, kern_bytes, kern_name = ms, 24.0 * n, "outer_fused<W=1> (flat_kernel)"
+        kern_ms, kern_bytes, kern_name = ms, 24.0 * n, "outer_fused<W=1> (tma::tile_kernel)"
+    elif mode == "p2p":
+        # the step IS one launch of the fused kernel over this rank's shard (+ two flag barriers);
+        # HBM bytes this GPU moves for it: its copy is read once and written once by the W owners
+        # (8 B/elem) and it reads+writes its master and momentum shards (16/W B/elem)
+        kern_ms, kern_bytes = ms, (8.0 + 16.0 / world) * n
+        kern_name = f"outer_fused<W={world}> over peer memory (tma::tile_kernel), NVLink-bound"
     else:
         k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
@@ -327,13 +351,16 @@ def native_arm(args):
                 "algorithmic_bytes_per_launch": kern_bytes, "kernel_ms": kern_ms}
 
     # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
-    hbm_bytes = (24.0 if world == 1 else 12.0 + 24.0 / world) * n
+    hbm_bytes = (24.0 if world == 1 else (8.0 + 16.0 / world if mode == "p2p" else 12.0 + 24.0 / world)) * n
     nvl_bytes = 0.0 if world == 1 else 8.0 * (world - 1) / world * n
     step_roof = {"hbm_algorithmic_gbs": hbm_bytes / (ms * 1e-3) / 1e9,
                  "nvlink_algorithmic_gbs_per_dir": nvl_bytes / (ms * 1e-3) / 1e9,
                  "t_hbm_ms": hbm_bytes / (peak * 1e9) * 1e3, "t_nvlink_ms_at_900": nvl_bytes / 900e9 * 1e3}
     bound_ms = max(step_roof["t_hbm_ms"], step_roof["t_nvlink_ms_at_900"])
     step_roof["frac_of_overlapped_bound"] = bound_ms / ms
+    step_roof["t_nvlink_ms_at_770_measured_peer_copy"] = nvl_bytes / 770e9 * 1e3
+    step_roof["frac_of_bound_at_770"] = max(step_roof["t_hbm_ms"], nvl_bytes / 770e9 * 1e3) / ms
+    step_roof["sync"] = mode
 
     # ---- e2e: last-sync copy in pinned HOST memory, H2D + D2H inside the timed region ------------
     e2e = None
@@ -371,7 +398,9 @@ def native_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 3, 1, budget_s=args.cpu_budget_s)
 
-    if world > 1:
+    if mode == "p2p":
+        launches_per_step = 3                                          # barrier, fused kernel, barrier
+    elif world > 1:
         launches_per_step = 2 * ((n + ctx.bucket - 1) // ctx.bucket)   # K1 + K2 per bucket
     else:
         launches_per_step = 1
@@ -385,10 +414,13 @@ def native_arm(args):
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
             "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
-            "bucket_mb": args.bucket_mb if world > 1 else None,
+            "bucket_mb": args.bucket_mb if mode == "nccl" else None, "sync": mode,
         }
         print(json.dumps(line), flush=True)
-    ctx.close()
+    if ctx is not None:
+        ctx.close()
+    if pctx is not None:
+        pctx.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -404,6 +436,8 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="llama1b")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--streams", type=int, default=2)
+    ap.add_argument("--sync", choices=["p2p", "nccl"], default="p2p",
+                    help="N>1: fused peer-memory kernel (default) or bucketed NCCL reduce-scatter/all-gather")
     ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)

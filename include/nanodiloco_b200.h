@@ -225,6 +225,49 @@ int nd_outer_step_offloaded(nd_sync_ctx* ctx, float* master_host, float* staging
  * promised. */
 int nd_sync_last_ms(nd_sync_ctx* ctx, float* ms_out);
 
+/* ---- peer-memory outer sync: one kernel per GPU over NVLink --------------------- */
+
+#define ND_IPC_HANDLE_BYTES 64 /* sizeof(cudaIpcMemHandle_t) */
+
+/* Allocates this rank's SHARED working-parameter buffer (device memory every rank of the node
+ * can map; zero-filled; `bytes` of payload followed by a flag page used by the barrier) and
+ * returns its CUDA IPC handle for the host to pass to the other ranks (torch.distributed
+ * all_gather / a store).  This is the one place the library allocates memory the caller sees:
+ * IPC needs cudaMalloc'ed memory.  Free with nd_peer_free after nd_peer_ctx_destroy. */
+int nd_peer_alloc(size_t bytes, void** dev_ptr_out, char handle_out[ND_IPC_HANDLE_BYTES]);
+int nd_peer_free(void* dev_ptr);
+
+typedef struct nd_peer_ctx nd_peer_ctx;
+
+/* handles_host: world * ND_IPC_HANDLE_BYTES bytes, the handle of every rank in rank order (this
+ * rank's own entry is ignored).  Maps the peers' buffers (cudaIpcOpenMemHandle with lazy peer
+ * access).  world <= ND_MAX_WORKERS; all ranks on one NVLink/NVSwitch domain. */
+int nd_peer_ctx_create(int world, int rank, void* my_buffer, size_t bytes, const char* handles_host,
+                       nd_peer_ctx** out);
+int nd_peer_ctx_destroy(nd_peer_ctx* ctx);
+/* Address, in this process, of rank w's buffer. */
+int nd_peer_buffer(const nd_peer_ctx* ctx, int w, void** out);
+/* Device-side barrier over the ranks (flag exchange in peer memory), enqueued on `stream`.
+ * Every rank must enqueue the same sequence of barriers. */
+int nd_peer_barrier(nd_peer_ctx* ctx, nd_stream_t stream);
+
+/* The whole outer step of diloco.py:34-54 across `world` GPUs as one fused kernel per GPU:
+ *   barrier -> nd_outer_fused over this rank's shard [rank*n/W, (rank+1)*n/W) with the W worker
+ *   copies addressed through peer memory (reads AND the copy-back go over NVLink inside the
+ *   kernel) -> barrier.
+ * The working parameters of every rank are the first n_padded elements of its shared buffer.
+ * master_shard / mom_shard: this rank's n_padded/W elements of last-sync copy and outer momentum
+ * (ordinary device memory; there is no replica of either).  n_padded: multiple of 4*world
+ * (8*world for a bf16 working copy).  The average is summed in worker order 0..W-1 on every
+ * shard, so all ranks end bit-identical and results do not depend on timing.
+ * sumsq_out/scratch as in nd_outer_fused (this rank's shard only).  Replaces the collective of
+ * diloco.py:49 together with :46-54. */
+int nd_outer_sync_p2p(nd_peer_ctx* ctx, float* master_shard, float* mom_shard, int local_dtype,
+                      int64_t n_padded, float lr, float mu, float dampening, float wd,
+                      int nesterov, int first_step, float* sumsq_out, void* scratch,
+                      nd_stream_t stream);
+int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
+
 #ifdef __cplusplus
 }
 #endif

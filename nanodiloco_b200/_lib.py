@@ -15,6 +15,7 @@ ND_F32, ND_BF16 = 0, 1
 ND_CHUNK = 16384
 ND_MAX_WORKERS = 16
 ND_UNIQUE_ID_BYTES = 128
+ND_IPC_HANDLE_BYTES = 64
 
 _c_i64 = ctypes.c_int64
 _c_f = ctypes.c_float
@@ -49,6 +50,15 @@ SIGNATURES = {
     "nd_outer_step_offloaded": (_c_i, [_c_p, _c_p, _c_p, _c_i64, _c_p, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f,
                                        _c_i, _c_i, _c_p]),
     "nd_sync_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
+    "nd_peer_alloc": (_c_i, [ctypes.c_size_t, ctypes.POINTER(_c_p), ctypes.c_char_p]),
+    "nd_peer_free": (_c_i, [_c_p]),
+    "nd_peer_ctx_create": (_c_i, [_c_i, _c_i, _c_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.POINTER(_c_p)]),
+    "nd_peer_ctx_destroy": (_c_i, [_c_p]),
+    "nd_peer_buffer": (_c_i, [_c_p, _c_i, ctypes.POINTER(_c_p)]),
+    "nd_peer_barrier": (_c_i, [_c_p, _c_p]),
+    "nd_outer_sync_p2p": (_c_i, [_c_p, _c_p, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p, _c_p,
+                                 _c_p]),
+    "nd_peer_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
 }
 
 _lib: Optional[ctypes.CDLL] = None

@@ -12,7 +12,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libnanodiloco_b200.so")
-SOURCES = ["nd_kernels.cu", "nd_sync.cu"]
+SOURCES = ["nd_kernels.cu", "nd_sync.cu", "nd_peer.cu"]
 HEADERS = ["nd_common.cuh", "nd_error.h", "nd_tma.cuh", os.path.join("..", "..", "include", "nanodiloco_b200.h")]
 
 NVCC_FLAGS = [

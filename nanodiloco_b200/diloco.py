@@ -71,6 +71,7 @@ class Diloco:
         max_grad_norm: float = 1.0,
         offload_master: bool = False,
         offload_chunk_mb: float = 64.0,
+        sync: str = "auto",
     ):
         # diloco.py:17-20
         self.model = model
@@ -111,7 +112,20 @@ class Diloco:
         W = self.world_size
         self.layout = FlatLayout.plan(self._params, quantum=4 * W)
         n = self.layout.total
-        self._local = torch.zeros(n, dtype=torch.float32, device=dev)
+        # How the W worker copies meet (W > 1):
+        #   "p2p"  one fused kernel per GPU over NVLink peer memory (nd_outer_sync_p2p); needs every
+        #          rank on one node with peer access.  Master and momentum are sharded 1/W.
+        #   "nccl" bucketed reduce-scatter -> shard update -> all-gather (nd_outer_sync).
+        if sync not in ("auto", "p2p", "nccl"):
+            raise ValueError("sync must be 'auto', 'p2p' or 'nccl'")
+        self.sync_mode = "none" if W == 1 else (self._pick_sync_mode(dev) if sync == "auto" else sync)
+        self._peer = None
+        if self.sync_mode == "p2p":
+            from .sync import PeerContext
+            self._peer = PeerContext(W, self.rank, n, group=process_group, device=dev)
+            self._local = self._peer.local(torch.float32)[:n]
+        else:
+            self._local = torch.zeros(n, dtype=torch.float32, device=dev)
         rehome_(self._params, self._local, self.layout)
 
         # diloco.py:21-22: every worker starts from rank 0's parameters (one flat broadcast
@@ -136,12 +150,19 @@ class Diloco:
             self._off_ctx = SyncContext(1, 0, bucket_elems=self._off_chunk, n_streams=max(3, n_streams),
                                         device=dev)
             self._staging = torch.empty(max(3, n_streams) * self._off_chunk, dtype=torch.float32, device=dev)
+        elif self._peer is not None:
+            lo, hi = self._peer.shard_range()
+            self._master = self._local[lo:hi].clone()       # this rank's shard only: no replica
         else:
             self._master = self._local.clone()
 
         # ---- sharded sync context -------------------------------------------------------------
         self._ctx = None
-        if W > 1:
+        if self._peer is not None:
+            lo, hi = self._peer.shard_range()
+            self._mom = torch.zeros(hi - lo, dtype=torch.float32, device=dev)
+            self._pg = None
+        elif W > 1:
             from .sync import SyncContext
             self._ctx = SyncContext(W, self.rank, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
                                     n_streams=n_streams, group=process_group, device=dev)
@@ -199,10 +220,27 @@ class Diloco:
         for p, gv in zip(self._params, self._grad_views):
             p.grad = gv
 
+    def _pick_sync_mode(self, dev) -> str:
+        """'p2p' when every rank sits on this node and can map every other rank's memory."""
+        import socket
+        info = [None] * self.world_size
+        dist.all_gather_object(info, (socket.gethostname(), dev.index), group=self._pg_group)
+        same_host = len({h for h, _ in info}) == 1
+        ok = same_host and self.world_size <= _lib.ND_MAX_WORKERS and len({i for _, i in info}) == self.world_size
+        if ok:
+            ok = all(i == dev.index or torch.cuda.can_device_access_peer(dev.index, i) for _, i in info)
+        votes = [None] * self.world_size
+        dist.all_gather_object(votes, bool(ok), group=self._pg_group)
+        return "p2p" if all(votes) else "nccl"
+
     @property
     def offloaded_last_sync_parameters(self) -> List[torch.Tensor]:
         """theta_sync per tensor (diloco.py:25,54) -- views of the master copy (HBM-resident, or
-        host-resident with `offload_master=True`; then synchronise the stream before reading)."""
+        host-resident with `offload_master=True`; then synchronise the stream before reading).
+        With the peer-memory sync each rank holds 1/W of it, so reading this property is a
+        COLLECTIVE (all ranks must read it together)."""
+        if self._peer is not None:
+            return self.layout.views(self._peer.gather_shards(self._master))
         return self.layout.views(self._master)
 
     def _get_offloaded_parameters(self):  # diloco.py:27-32, for callers that used it
@@ -230,6 +268,14 @@ class Diloco:
                                                dampening=float(g["dampening"]),
                                                weight_decay=float(g["weight_decay"]),
                                                nesterov=bool(g["nesterov"]), first_step=first)
+        elif self._peer is not None:
+            if len(self._outer_ranges) != 1:
+                raise NotImplementedError("the sharded outer sync supports a single outer param group")
+            g = self._outer_ranges[0][0]
+            self._check_outer_group(g)
+            self._peer.outer_sync(self._master, self._mom, lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                  dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
+                                  nesterov=bool(g["nesterov"]), first_step=first)
         elif self._ctx is None:
             for g, s, e in self._outer_ranges:
                 self._check_outer_group(g)
@@ -260,16 +306,19 @@ class Diloco:
     def _publish_outer_state(self) -> None:
         """outer_optimizer.state[p]['momentum_buffer'] as views (world size 1).  With the
         sharded sync each rank holds 1/W of the momentum; `gather_outer_state()` assembles it."""
-        if self._ctx is not None:
+        if self._ctx is not None or self._peer is not None:
             return
         for p, v in zip(self._params, self.layout.views(self._mom)):
             self.outer_optimizer.state[p]["momentum_buffer"] = v
 
     def gather_outer_state(self) -> None:
         """Collective: materialise the full momentum buffers into outer_optimizer.state."""
-        if self._ctx is None:
+        if self._ctx is None and self._peer is None:
             return self._publish_outer_state()
-        full = self._ctx.gather_shards(self._mom, self.layout.total)
+        if self._peer is not None:
+            full = self._peer.gather_shards(self._mom)
+        else:
+            full = self._ctx.gather_shards(self._mom, self.layout.total)
         for p, v in zip(self._params, self.layout.views(full)):
             self.outer_optimizer.state[p]["momentum_buffer"] = v
 

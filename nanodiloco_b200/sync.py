@@ -103,3 +103,97 @@ class SyncContext:
             self.close()
         except Exception:
             pass
+
+
+class _RawDeviceBuffer:
+    """A device allocation owned by the C library, exposed to torch through the CUDA array interface."""
+
+    def __init__(self, ptr: int, nbytes: int):
+        self.ptr, self.nbytes = ptr, nbytes
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerContext:
+    """Host side of the peer-memory outer sync (include/nanodiloco_b200.h, `nd_outer_sync_p2p`).
+
+    Allocates this rank's shared working-parameter buffer, exchanges CUDA IPC handles over the torch
+    process group (plumbing only) and maps the peers' buffers.  `local(dtype)` is the torch view of
+    the shared buffer: parameters re-homed into it are readable and writable by every rank's kernel.
+    """
+
+    def __init__(self, world: int, rank: int, n_padded: int, *, elem_bytes: int = 4, group=None, device=None):
+        L = _lib.load()
+        self.world, self.rank, self.group = world, rank, group
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.n_padded = int(n_padded)
+        self.nbytes = self.n_padded * elem_bytes
+        ptr = ctypes.c_void_p()
+        handle = ctypes.create_string_buffer(_lib.ND_IPC_HANDLE_BYTES)
+        with torch.cuda.device(self.device):
+            _lib.check(L.nd_peer_alloc(self.nbytes, ctypes.byref(ptr), handle), "nd_peer_alloc")
+            self._ptr = ptr.value
+            handles = [None] * world
+            if world > 1:
+                dist.all_gather_object(handles, handle.raw, group=group)
+            else:
+                handles[0] = handle.raw
+            blob = ctypes.create_string_buffer(b"".join(handles), world * _lib.ND_IPC_HANDLE_BYTES)
+            h = ctypes.c_void_p()
+            _lib.check(L.nd_peer_ctx_create(world, rank, self._ptr, self.nbytes, blob, ctypes.byref(h)),
+                       "nd_peer_ctx_create")
+        self._h = h
+        self._raw = _RawDeviceBuffer(self._ptr, self.nbytes)
+        self._bytes = torch.as_tensor(self._raw, device=self.device)
+
+    def local(self, dtype=torch.float32) -> torch.Tensor:
+        return self._bytes.view(dtype)
+
+    def peer_view(self, w: int, dtype=torch.float32) -> torch.Tensor:
+        """Rank w's buffer as mapped into this process (tests / debugging)."""
+        p = ctypes.c_void_p()
+        _lib.check(_lib.load().nd_peer_buffer(self._h, w, ctypes.byref(p)), "nd_peer_buffer")
+        raw = _RawDeviceBuffer(p.value, self.nbytes)
+        t = torch.as_tensor(raw, device=self.device).view(dtype)
+        t._nd_keepalive = (raw, self)
+        return t
+
+    def shard_range(self, rank=None):
+        r = self.rank if rank is None else rank
+        s = self.n_padded // self.world
+        return r * s, (r + 1) * s
+
+    def barrier(self, stream=None) -> None:
+        _lib.check(_lib.load().nd_peer_barrier(self._h, _lib._stream(stream)), "nd_peer_barrier")
+
+    def outer_sync(self, master_shard, mom_shard, *, dtype=torch.float32, lr, momentum, dampening=0.0,
+                   weight_decay=0.0, nesterov=True, first_step=False, sumsq_out=None, scratch_buf=None,
+                   stream=None) -> None:
+        _lib._require_cuda(master_shard, mom_shard, sumsq_out, scratch_buf)
+        code = _lib.ND_BF16 if dtype == torch.bfloat16 else _lib.ND_F32
+        _lib.check(_lib.load().nd_outer_sync_p2p(self._h, _lib._ptr(master_shard), _lib._ptr(mom_shard), code,
+                                                 self.n_padded, lr, momentum, dampening, weight_decay,
+                                                 int(nesterov), int(first_step), _lib._ptr(sumsq_out),
+                                                 _lib._ptr(scratch_buf), _lib._stream(stream)),
+                   "nd_outer_sync_p2p")
+
+    def last_ms(self) -> float:
+        ms = ctypes.c_float()
+        _lib.check(_lib.load().nd_peer_last_ms(self._h, ctypes.byref(ms)), "nd_peer_last_ms")
+        return float(ms.value)
+
+    def gather_shards(self, shard: torch.Tensor) -> torch.Tensor:
+        """Collective over the torch group: contiguous shards -> the full flat buffer."""
+        parts = [torch.empty_like(shard) for _ in range(self.world)]
+        if self.world > 1:
+            dist.all_gather(parts, shard, group=self.group)
+        else:
+            parts[0] = shard
+        return torch.cat(parts)
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize(self.device)
+            if self.world > 1 and dist.is_initialized():
+                dist.barrier(group=self.group)      # nobody unmaps while a peer may still touch the buffer
+            _lib.load().nd_peer_ctx_destroy(self._h)
+            self._h = None

@@ -8,7 +8,7 @@ CPU -- the reference's own CPU-runnable configuration (BASELINE.json configs[0])
     python tests/golden/make_golden.py            # writes tests/golden/*.npz
 
 Fixtures (all float32, flat concatenation of the tensors in `shapes` order):
-  outer_w{W}.npz  W in {1,2,4}; R=3 outer rounds
+  outer_w{W}.npz  W in {1,2,4,8}; R=3 outer rounds
       init                 params every worker starts from (seed 1337, main.py:43)
       local_r{r}_w{w}      worker w's params just before outer round r (inputs)
       params_r{r}          every worker's params after round r  (outputs)
@@ -138,8 +138,12 @@ if __name__ == "__main__":
     if not os.path.exists(REF):
         sys.exit("the reference is not mounted here; fixtures can only be generated in the build container")
     only_inner = "--inner-only" in sys.argv
-    for W in () if only_inner else (1, 2, 4):
+    worlds = (1, 2, 4, 8)
+    if "--only-w" in sys.argv:
+        worlds = (int(sys.argv[sys.argv.index("--only-w") + 1]),)
+    for W in () if only_inner else worlds:
         run(outer_worker, W, os.path.join(HERE, f"outer_w{W}.npz"))
         print("wrote", f"outer_w{W}.npz")
-    run(inner_worker, 1, os.path.join(HERE, "inner.npz"))
-    print("wrote inner.npz")
+    if "--only-w" not in sys.argv:
+        run(inner_worker, 1, os.path.join(HERE, "inner.npz"))
+        print("wrote inner.npz")

@@ -209,3 +209,26 @@ def test_full_size_properties():
     del before, delta, d, want
     # linearity checksum: sum of master == sum of local (bitwise equal arrays)
     assert float(master.double().sum()) == float(local.double().sum())
+
+
+# ---- peer-memory entry point on one GPU (world size 1: plumbing of the shared buffer) ------------
+
+def test_peer_context_world1_matches_oracle():
+    from nanodiloco_b200.sync import PeerContext
+    n = 40_004
+    ctx = PeerContext(1, 0, n, device=torch.device("cuda", 0))
+    local = ctx.local()[:n]
+    assert float(local.abs().max()) == 0.0 and local.data_ptr() % 256 == 0       # zero-filled, aligned
+    master_np, mom_np = _rand(n, 1, 0.02), _rand(n, 2, 1e-3)
+    loc_np = master_np + _rand(n, 3, 1e-3)
+    local.copy_(torch.from_numpy(loc_np))
+    assert torch.equal(ctx.peer_view(0)[:n], local)                              # same memory
+    master, mom = dev(master_np), dev(mom_np)
+    ctx.outer_sync(master, mom, lr=LR, momentum=MU)
+    O.outer_step(master_np, [loc_np], mom_np, lr=LR, momentum=MU)
+    torch.cuda.synchronize()
+    assert np.array_equal(host(master), master_np) and np.array_equal(host(local), master_np)
+    assert ctx.last_ms() > 0
+    ctx.barrier()                                                                # single-rank barrier returns
+    torch.cuda.synchronize()
+    ctx.close()

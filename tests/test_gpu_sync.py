@@ -1,6 +1,7 @@
-"""GPU, world size >= 2 (skipped on a single-GPU box): the sharded outer sync over NCCL
-(nd_outer_sync: K1 -> reduce-scatter -> K2 on the owned slice -> all-gather, bucketed) through the
-drop-in wrapper, against the reference's golden fixtures."""
+"""GPU, world size >= 2 (skipped on a single-GPU box): the multi-GPU outer sync through the drop-in
+wrapper against the reference's golden fixtures, both ways the worker copies can meet:
+  nccl  nd_outer_sync: K1 -> reduce-scatter -> K2 on the owned slice -> all-gather, bucketed
+  p2p   nd_outer_sync_p2p: one fused kernel per GPU over NVLink peer memory"""
 import os
 import tempfile
 
@@ -14,7 +15,7 @@ pytestmark = [pytest.mark.gpu, pytest.mark.timeout(600)]
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
-def _worker(rank, world, store, bucket_mb, result_path):
+def _worker(rank, world, store, bucket_mb, mode, result_path):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
     from test_gpu_diloco import Bag, _flat
@@ -30,7 +31,8 @@ def _worker(rank, world, store, bucket_mb, result_path):
                 p.add_(1.0)
     inner = torch.optim.AdamW(model.parameters(), lr=4e-4)
     outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
-    d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2)
+    d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2, sync=mode)
+    assert d.sync_mode == mode
     params = list(model.parameters())
     ok = np.array_equal(_flat(params).cpu().numpy(), z["init"])
     exact = world <= 2
@@ -52,6 +54,13 @@ def _worker(rank, world, store, bucket_mb, result_path):
             ok &= np.allclose(got, want, rtol=1e-6, atol=1e-6 * np.abs(want).max())
             ok &= np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max())
         ok &= np.array_equal(_flat(d.offloaded_last_sync_parameters).cpu().numpy(), got)
+        if mode == "p2p":   # fixed summation order: bit-exact against the oracle's order for ANY world size
+            from oracle import oracle as O
+            if r == 0:
+                om, ob = z["init"].copy(), np.zeros_like(z["init"])
+            O.outer_step(om, [z[f"local_r{r}_w{w}"].copy() for w in range(world)], ob, lr=0.7, momentum=0.9,
+                         first_step=(r == 0))
+            ok &= np.array_equal(got, om) and np.array_equal(mom, ob)
     ok &= d.avg_sync_time > 0
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
@@ -62,12 +71,12 @@ def _worker(rank, world, store, bucket_mb, result_path):
     dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 4])
-@pytest.mark.parametrize("bucket_mb", [0.002, 64.0])      # many tiny buckets / one bucket
-def test_sharded_outer_sync_vs_reference(world, bucket_mb):
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0)])
+def test_sharded_outer_sync_vs_reference(world, mode, bucket_mb):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
     with tempfile.TemporaryDirectory() as td:
         res = os.path.join(td, "res")
-        mp.spawn(_worker, args=(world, os.path.join(td, "store"), bucket_mb, res), nprocs=world, join=True)
+        mp.spawn(_worker, args=(world, os.path.join(td, "store"), bucket_mb, mode, res), nprocs=world, join=True)
         assert open(res).read() == "ok"

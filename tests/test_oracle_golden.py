@@ -33,15 +33,16 @@ def test_outer_step_bit_exact_vs_reference(golden_dir, W):
             assert np.array_equal(l, master)
 
 
-def test_outer_step_w4_within_tolerance(golden_dir):
-    """W=4: gloo's ring sums in a different order than worker order; the north-star tolerance
+@pytest.mark.parametrize("W", [4, 8])
+def test_outer_step_w4_w8_within_tolerance(golden_dir, W):
+    """W>=4: gloo's ring sums in a different order than worker order; the north-star tolerance
     (rtol 1e-6 on params and momentum) needs an atol floor because the pseudo-gradient is a
     difference of nearly equal numbers.  atol = 1e-6 * max|value|."""
-    z = np.load(os.path.join(golden_dir, "outer_w4.npz"))
+    z = np.load(os.path.join(golden_dir, f"outer_w{W}.npz"))
     master = z["init"].copy()
     buf = np.zeros_like(master)
     for r in range(3):
-        locs = [z[f"local_r{r}_w{w}"].copy() for w in range(4)]
+        locs = [z[f"local_r{r}_w{w}"].copy() for w in range(W)]
         O.outer_step(master, locs, buf, lr=OUTER_LR, momentum=OUTER_MU, first_step=(r == 0))
         for got, want in ((master, z[f"params_r{r}"]), (buf, z[f"mom_r{r}"])):
             np.testing.assert_allclose(got, want, rtol=1e-6, atol=1e-6 * np.abs(want).max())
