@@ -133,6 +133,24 @@ int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t to
 int nd_sumsq(const void* g, int dtype, int64_t n, float* out, void* scratch,
              nd_stream_t stream);
 
+/* nd_sumsq without caller scratch and without any allocation (no counterpart in the
+ * reference: it exists for how this library gets embedded, not for the algorithm).
+ * For callers that can pass inputs and outputs but cannot provide scratch or tolerate a
+ * cudaMalloc: a process whose HBM is entirely owned by another pool (a capped caching
+ * allocator, a server's fixed arena), a latency-critical loop that cannot afford the device-wide
+ * synchronisation hidden in cudaMalloc/cudaFree, or a thin FFI caller with no allocator of its
+ * own.  The partial sums live in a fixed ND_SUMSQ_STATIC_SCRATCH_BYTES array inside the library
+ * image (held by every GPU that loads the library until the process exits).
+ *   - out[0] = sum(g[i]^2) exactly as nd_sumsq computes it.
+ *   - n > ND_SUMSQ_STATIC_MAX_ELEMS is rejected with ND_EINVAL; use nd_sumsq beyond it.
+ *   - the first call on each device looks up the array's device address (set-up); make that
+ *     first call outside any stream capture.  No call allocates or frees memory.
+ *   - all calls on a device share the array: calls that overlap on the GPU race; order them
+ *     (same stream, or an event). */
+#define ND_SUMSQ_STATIC_SCRATCH_BYTES 8192
+#define ND_SUMSQ_STATIC_MAX_ELEMS (1LL << 31)
+int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t stream);
+
 /* Multi-tensor form: ptr[0]=grad. */
 int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
                 float* out, void* scratch, nd_stream_t stream);

@@ -36,6 +36,7 @@ SIGNATURES = {
                               _c_i, _c_i, _c_p, _c_p, _c_p]),
     "nd_outer_fused_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p]),
     "nd_sumsq": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
+    "nd_sumsq_static": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p]),
     "nd_sumsq_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
     "nd_adamw": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
                         _c_i, _c_p]),
@@ -177,6 +178,13 @@ def sumsq(g, out, scratch_buf, stream=None) -> None:
     _require_cuda(g, out, scratch_buf)
     check(load().nd_sumsq(_ptr(g), _dtype_code(g), g.numel(), _ptr(out), _ptr(scratch_buf), _stream(stream)),
           "nd_sumsq")
+
+
+def sumsq_static(g, out, stream=None) -> None:
+    """nd_sumsq_static: same result as `sumsq`, scratch inside the library, nothing allocated."""
+    _require_cuda(g, out)
+    check(load().nd_sumsq_static(_ptr(g), _dtype_code(g), g.numel(), _ptr(out), _stream(stream)),
+          "nd_sumsq_static")
 
 
 def adamw(p, g, m, v, *, lr: float, beta1: float = 0.9, beta2: float = 0.999, eps: float = 1e-8,

@@ -793,6 +793,59 @@ int nd_sumsq(const void* g, int dtype, int64_t n, float* out, void* scratch, nd_
     return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, scratch, out, s);
 }
 
+// ---- nd_sumsq_static: the sum of squares with no caller scratch and no allocation ------------
+//
+// Some users of this library can hand us their inputs and outputs but cannot give us scratch:
+//   * a trainer or server that has already given all of HBM to its own pool (torch's caching
+//     allocator under a hard memory cap, an inference server's fixed arena): a stray cudaMalloc
+//     from a helper library either fails or breaks their memory plan;
+//   * a latency-critical loop, where the device-wide synchronisation hidden inside
+//     cudaMalloc/cudaFree would stall every other stream of the process;
+//   * a thin FFI caller (ctypes, cgo, a DLPack consumer) that owns no allocator at all and only
+//     forwards tensors somebody else created.
+// For them the per-block partial sums and the arrival counter live in the array below, which is
+// part of the library image: every GPU that loads the library carries these bytes until the
+// process exits.  All calls on a device share it, so two calls that overlap on the GPU (different
+// streams without an event between them, or two host threads) race on it -- order them.
+static __device__ __align__(256) unsigned char g_sumsq_static_scratch[ND_SUMSQ_STATIC_SCRATCH_BYTES];
+static_assert(sizeof(Scratch) <= ND_SUMSQ_STATIC_SCRATCH_BYTES, "static scratch too small for nd::Scratch");
+
+// In host code `g_sumsq_static_scratch` is only a handle for the runtime, not a device address:
+// the address a kernel can use comes from cudaGetSymbolAddress, looked up once per device with
+// that device current.
+static void* g_sumsq_static_ptr[64];
+
+int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    if (n > (int64_t)ND_SUMSQ_STATIC_MAX_ELEMS)
+        return set_error(ND_EINVAL, "nd_sumsq_static: n = %lld exceeds ND_SUMSQ_STATIC_MAX_ELEMS = %lld; "
+                                    "use nd_sumsq with caller-provided scratch",
+                         (long long)n, (long long)ND_SUMSQ_STATIC_MAX_ELEMS);
+    ND_REQUIRE((n == 0 || g) && out, "null pointer");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
+    int dev = 0;
+    ND_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return set_error(ND_EINVAL, "nd_sumsq_static: device index %d out of range", dev);
+    if (!g_sumsq_static_ptr[dev]) {  // set-up: first call on this device
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_sumsq_static_scratch);
+        if (e != cudaSuccess || !p)
+            return set_error(ND_ECUDA, "nd_sumsq_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
+        g_sumsq_static_ptr[dev] = p;
+    }
+    Scratch* sc = static_cast<Scratch*>(g_sumsq_static_ptr[dev]);
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    // the array keeps whatever the previous call (or a call that died half-way) left behind: the
+    // arrival counter is the one field that must be zero when the kernel starts
+    ND_CUDA(cudaMemsetAsync(&sc->counter, 0, sizeof(unsigned), s));
+    if (dtype == ND_BF16) {
+        SumsqOp<true> op{g, 0.f};
+        return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, sc, out, s);
+    }
+    SumsqOp<false> op{g, 0.f};
+    return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, sc, out, s);
+}
+
 int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, float* out, void* scratch,
                 nd_stream_t stream) {
     ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
