@@ -390,6 +390,34 @@ def native_arm(args):
                        "streamed H2D -> fused kernel -> D2H in %.0f MiB chunks over 3 streams" % args.offload_chunk_mb}
         octx.close()
         del master_host, staging
+    elif mode == "p2p":
+        Ke = max(2, min(K, args.e2e_steps))
+        shard = master.numel()
+        chunk = max(4, min(int(args.offload_chunk_mb * (1 << 20)) // 4, shard) // 4 * 4)
+        master_host = torch.empty(shard, dtype=torch.float32, pin_memory=True)
+        master_host.copy_(master)
+        staging = torch.empty(3 * chunk, device=dev)
+        for _ in range(2):
+            pctx.outer_sync_offloaded(master_host, staging, chunk, mom, **hyper)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        if sampler:
+            sampler.start()
+        e0.record()
+        for _ in range(Ke):
+            pctx.outer_sync_offloaded(master_host, staging, chunk, mom, **hyper)
+        e1.record()
+        barrier()
+        if sampler:
+            sampler.stop()
+        e_ms = torch.tensor([e0.elapsed_time(e1) / Ke], device=dev, dtype=torch.float64)
+        dist.all_reduce(e_ms, op=dist.ReduceOp.MAX)
+        e2e = {"value": float(e_ms), "unit": UNIT, "h2d_bytes_per_step": 4 * shard * world,
+               "d2h_bytes_per_step": 4 * shard * world, "steps": Ke,
+               "what": "nd_outer_sync_p2p_offloaded: every rank's 1/W master shard in pinned host memory (the "
+                       "reference keeps the last-sync copy on the host), streamed H2D -> fused peer kernel -> D2H in "
+                       "%.0f MiB chunks over 3 streams; bytes are the whole job's (all ranks)" % (chunk * 4 / 2**20)}
+        del master_host, staging
     if sampler:
         sampler.close()
 

@@ -284,6 +284,14 @@ int nd_outer_sync_p2p(nd_peer_ctx* ctx, float* master_shard, float* mom_shard, i
                       int64_t n_padded, float lr, float mu, float dampening, float wd,
                       int nesterov, int first_step, float* sumsq_out, void* scratch,
                       nd_stream_t stream);
+/* nd_outer_sync_p2p with this rank's master shard resident in page-locked HOST memory, where the
+ * reference keeps the last-sync copy (diloco.py:25-32,47,54): the shard is streamed in chunks
+ * (H2D -> fused peer kernel on the chunk -> D2H) over three internal side streams, between the two
+ * barriers.  staging: device buffer of 3 * chunk_elems floats.  Any world size >= 1. */
+int nd_outer_sync_p2p_offloaded(nd_peer_ctx* ctx, float* master_host_shard, float* staging,
+                                int64_t chunk_elems, float* mom_shard, int local_dtype,
+                                int64_t n_padded, float lr, float mu, float dampening, float wd,
+                                int nesterov, int first_step, nd_stream_t stream);
 int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
 
 #ifdef __cplusplus

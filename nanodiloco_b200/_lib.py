@@ -59,6 +59,8 @@ SIGNATURES = {
     "nd_peer_barrier": (_c_i, [_c_p, _c_p]),
     "nd_outer_sync_p2p": (_c_i, [_c_p, _c_p, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p, _c_p,
                                  _c_p]),
+    "nd_outer_sync_p2p_offloaded": (_c_i, [_c_p, _c_p, _c_p, _c_i64, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f,
+                                           _c_i, _c_i, _c_p]),
     "nd_peer_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
 }
 

@@ -56,6 +56,11 @@ struct nd_peer_ctx {
     uint32_t epoch = 0;
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timed = false;
+    // side streams for the host-resident-master variant (created on first use)
+    static constexpr int kStreams = 3;
+    cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr};
+    cudaEvent_t done[kStreams] = {nullptr, nullptr, nullptr};
+    cudaEvent_t fork = nullptr;
 };
 
 extern "C" {
@@ -122,6 +127,11 @@ int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     if (!c) return ND_OK;
     for (int w = 0; w < c->world; ++w)
         if (w != c->rank && c->base[w]) cudaIpcCloseMemHandle(c->base[w]);
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
+        if (c->streams[i]) cudaStreamDestroy(c->streams[i]);
+        if (c->done[i]) cudaEventDestroy(c->done[i]);
+    }
+    if (c->fork) cudaEventDestroy(c->fork);
     if (c->flag_pages_dev) cudaFree(c->flag_pages_dev);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
@@ -166,6 +176,62 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
                         first_step, sumsq_out, scratch, stream_);
     if (rc) return rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every shard of our copy has been written
+    ND_CUDA(cudaEventRecord(c->t1, stream));
+    c->timed = true;
+    return ND_OK;
+}
+
+int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float* staging, int64_t chunk_elems,
+                                float* mom_shard, int local_dtype, int64_t n_padded, float lr, float mu,
+                                float dampening, float wd, int nesterov, int first_step, nd_stream_t stream_) {
+    if (!c) return set_error(ND_ESTATE, "nd_outer_sync_p2p_offloaded: null context");
+    const int W = c->world;
+    if (local_dtype != ND_F32 && local_dtype != ND_BF16)
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: unknown dtype");
+    const int gran = local_dtype == ND_BF16 ? 8 : 4;
+    if (n_padded < 0 || n_padded % ((int64_t)gran * W) != 0)
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: n_padded must be a multiple of %d*world", gran);
+    if (chunk_elems < gran || chunk_elems % gran != 0)
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: chunk_elems must be a positive multiple of %d", gran);
+    const size_t esz = local_dtype == ND_BF16 ? 2 : 4;
+    if ((size_t)n_padded * esz > c->bytes)
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: n_padded exceeds the peer buffers");
+    if (n_padded && (!master_host_shard || !staging || !mom_shard))
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: null pointer");
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (!c->fork) {  // first use: side streams and the events that join them to the caller's stream
+        for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
+            ND_CUDA(cudaStreamCreateWithFlags(&c->streams[i], cudaStreamNonBlocking));
+            ND_CUDA(cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming));
+        }
+        ND_CUDA(cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming));
+    }
+    const int64_t shard = n_padded / W;
+    ND_CUDA(cudaEventRecord(c->t0, stream));
+    int rc;
+    if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
+    ND_CUDA(cudaEventRecord(c->fork, stream));
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) ND_CUDA(cudaStreamWaitEvent(c->streams[i], c->fork, 0));
+    int64_t k = 0;
+    for (int64_t off = 0; off < shard; off += chunk_elems, ++k) {
+        const int64_t len = (shard - off < chunk_elems) ? (shard - off) : chunk_elems;
+        const int slot = (int)(k % nd_peer_ctx::kStreams);
+        cudaStream_t s = c->streams[slot];  // stream order also keeps a slot from being reused too early
+        float* m_dev = staging + (int64_t)slot * chunk_elems;
+        ND_CUDA(cudaMemcpyAsync(m_dev, master_host_shard + off, (size_t)len * 4, cudaMemcpyHostToDevice, s));
+        void* locals[ND_MAX_WORKERS];
+        for (int w = 0; w < W; ++w)
+            locals[w] = static_cast<char*>(c->base[w]) + ((size_t)c->rank * shard + (size_t)off) * esz;
+        rc = nd_outer_fused(m_dev, mom_shard + off, locals, W, local_dtype, len, lr, mu, dampening, wd, nesterov,
+                            first_step, nullptr, nullptr, reinterpret_cast<nd_stream_t>(s));
+        if (rc) return rc;
+        ND_CUDA(cudaMemcpyAsync(master_host_shard + off, m_dev, (size_t)len * 4, cudaMemcpyDeviceToHost, s));
+    }
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
+        ND_CUDA(cudaEventRecord(c->done[i], c->streams[i]));
+        ND_CUDA(cudaStreamWaitEvent(stream, c->done[i], 0));
+    }
+    if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
     return ND_OK;

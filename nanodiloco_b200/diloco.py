@@ -141,15 +141,17 @@ class Diloco:
         self._first_outer = True
         self._scratch = _lib.scratch(dev)
         if offload_master:
-            if W > 1:
-                raise NotImplementedError("offload_master is implemented for world size 1")
+            if W > 1 and self._peer is None:
+                raise NotImplementedError("offload_master with several workers needs sync='p2p'")
             from .sync import SyncContext
-            self._master = torch.empty(n, dtype=torch.float32, pin_memory=True)
-            self._master.copy_(self._local)
-            self._off_chunk = max(4, int(offload_chunk_mb * (1 << 20)) // 4 // 4 * 4)
-            self._off_ctx = SyncContext(1, 0, bucket_elems=self._off_chunk, n_streams=max(3, n_streams),
-                                        device=dev)
-            self._staging = torch.empty(max(3, n_streams) * self._off_chunk, dtype=torch.float32, device=dev)
+            lo, hi = self._peer.shard_range() if self._peer is not None else (0, n)
+            self._master = torch.empty(hi - lo, dtype=torch.float32, pin_memory=True)
+            self._master.copy_(self._local[lo:hi])
+            self._off_chunk = max(4, min(int(offload_chunk_mb * (1 << 20)) // 4, hi - lo) // 4 * 4)
+            self._off_ctx = None
+            if self._peer is None:
+                self._off_ctx = SyncContext(1, 0, bucket_elems=self._off_chunk, n_streams=3, device=dev)
+            self._staging = torch.empty(3 * self._off_chunk, dtype=torch.float32, device=dev)
         elif self._peer is not None:
             lo, hi = self._peer.shard_range()
             self._master = self._local[lo:hi].clone()       # this rank's shard only: no replica
@@ -240,7 +242,11 @@ class Diloco:
         With the peer-memory sync each rank holds 1/W of it, so reading this property is a
         COLLECTIVE (all ranks must read it together)."""
         if self._peer is not None:
-            return self.layout.views(self._peer.gather_shards(self._master))
+            shard = self._master
+            if self.offload_master:
+                torch.cuda.current_stream(self.device).synchronize()
+                shard = shard.to(self.device)
+            return self.layout.views(self._peer.gather_shards(shard))
         return self.layout.views(self._master)
 
     def _get_offloaded_parameters(self):  # diloco.py:27-32, for callers that used it
@@ -263,11 +269,13 @@ class Diloco:
                 raise NotImplementedError("offload_master supports a single outer param group")
             g = self._outer_ranges[0][0]
             self._check_outer_group(g)
-            self._off_ctx.outer_step_offloaded(self._master, self._staging, self._off_chunk, self._mom,
-                                               self._local, lr=float(g["lr"]), momentum=float(g["momentum"]),
-                                               dampening=float(g["dampening"]),
-                                               weight_decay=float(g["weight_decay"]),
-                                               nesterov=bool(g["nesterov"]), first_step=first)
+            kw = dict(lr=float(g["lr"]), momentum=float(g["momentum"]), dampening=float(g["dampening"]),
+                      weight_decay=float(g["weight_decay"]), nesterov=bool(g["nesterov"]), first_step=first)
+            if self._peer is not None:
+                self._peer.outer_sync_offloaded(self._master, self._staging, self._off_chunk, self._mom, **kw)
+            else:
+                self._off_ctx.outer_step_offloaded(self._master, self._staging, self._off_chunk, self._mom,
+                                                   self._local, **kw)
         elif self._peer is not None:
             if len(self._outer_ranges) != 1:
                 raise NotImplementedError("the sharded outer sync supports a single outer param group")

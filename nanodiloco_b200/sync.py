@@ -176,6 +176,19 @@ class PeerContext:
                                                  _lib._ptr(scratch_buf), _lib._stream(stream)),
                    "nd_outer_sync_p2p")
 
+    def outer_sync_offloaded(self, master_host_shard, staging, chunk_elems, mom_shard, *, dtype=torch.float32,
+                             lr, momentum, dampening=0.0, weight_decay=0.0, nesterov=True, first_step=False,
+                             stream=None) -> None:
+        """nd_outer_sync_p2p_offloaded: this rank's master shard in pinned host memory."""
+        if master_host_shard.is_cuda or not master_host_shard.is_pinned():
+            raise _lib.NDError("master_host_shard must be page-locked host memory")
+        _lib._require_cuda(staging, mom_shard)
+        code = _lib.ND_BF16 if dtype == torch.bfloat16 else _lib.ND_F32
+        _lib.check(_lib.load().nd_outer_sync_p2p_offloaded(
+            self._h, master_host_shard.data_ptr(), _lib._ptr(staging), int(chunk_elems), _lib._ptr(mom_shard), code,
+            self.n_padded, lr, momentum, dampening, weight_decay, int(nesterov), int(first_step),
+            _lib._stream(stream)), "nd_outer_sync_p2p_offloaded")
+
     def last_ms(self) -> float:
         ms = ctypes.c_float()
         _lib.check(_lib.load().nd_peer_last_ms(self._h, ctypes.byref(ms)), "nd_peer_last_ms")

@@ -31,8 +31,10 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
                 p.add_(1.0)
     inner = torch.optim.AdamW(model.parameters(), lr=4e-4)
     outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
-    d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2, sync=mode)
-    assert d.sync_mode == mode
+    sync = "p2p" if mode.startswith("p2p") else mode
+    extra = dict(offload_master=True, offload_chunk_mb=0.001) if mode == "p2p_offload" else {}
+    d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2, sync=sync, **extra)
+    assert d.sync_mode == sync
     params = list(model.parameters())
     ok = np.array_equal(_flat(params).cpu().numpy(), z["init"])
     exact = world <= 2
@@ -54,7 +56,7 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
             ok &= np.allclose(got, want, rtol=1e-6, atol=1e-6 * np.abs(want).max())
             ok &= np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max())
         ok &= np.array_equal(_flat(d.offloaded_last_sync_parameters).cpu().numpy(), got)
-        if mode == "p2p":   # fixed summation order: bit-exact against the oracle's order for ANY world size
+        if mode.startswith("p2p"):   # fixed summation order: bit-exact against the oracle's order for ANY world size
             from oracle import oracle as O
             if r == 0:
                 om, ob = z["init"].copy(), np.zeros_like(z["init"])
@@ -72,7 +74,7 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0)])
+@pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_offload", 64.0)])
 def test_sharded_outer_sync_vs_reference(world, mode, bucket_mb):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
