@@ -18,6 +18,6 @@ echo "launch list rc=$?"
 echo "== ncu full capture (150M-class model so that 40 replays stay short)"
 CMD2="python bench.py --workload llama150m --steps 3 --warmup 3 --no-cpu-baseline --e2e-steps 2"
 timeout 600 $CMD2 > $OUT/plain150_$TAG.log 2>&1 &&
-timeout 1200 ncu --set full --clock-control none --import-source on -k regex:flat_kernel -s 4 -c 2 -o $OUT/prof_$TAG -f $CMD2 > $OUT/ncu_full_$TAG.log 2>&1
+timeout 1200 ncu --set full --clock-control none --import-source on -k regex:tile_kernel -s 4 -c 2 -o $OUT/prof_$TAG -f $CMD2 > $OUT/ncu_full_$TAG.log 2>&1
 echo "full capture rc=$?"
 ls -la $OUT
