@@ -355,6 +355,8 @@ class Diloco:
                        sumsq_dev=self._sumsq, max_norm=self.max_grad_norm, zero_grad=True)
         for p in self._params:
             self.inner_optimizer.state[p]["step"] += 1
+        # the fused kernel stood in for inner_optimizer.step(); tell the LR scheduler's order check so
+        self.inner_optimizer._opt_called = True
         self.scheduler.step()
         # diloco.py:60 zero_grad(): fused into the AdamW pass; .grad stays a (zeroed) view of the
         # flat gradient buffer so the next backward accumulates straight into it.

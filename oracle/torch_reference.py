@@ -80,3 +80,27 @@ CONFIGS = {
     "llama150m": dict(hidden=1024, inter=2688, layers=12),
     "llama1b": dict(hidden=2048, inter=5632, layers=22),
 }
+
+
+class ReferenceDilocoModelPort(ReferenceDilocoPort):
+    """The port with the reference class's full surface (diloco.py:8-16,66-74): built from a model,
+    callable, train()/eval() -- so it can stand where `Diloco` stands in the training loop."""
+
+    def __init__(self, model, inner_optimizer, outer_optimizer, warmup_steps, total_steps,
+                 inner_steps: int = 100, outer_steps: int = 10):
+        self.model = model
+        super().__init__(list(model.parameters()), inner_optimizer, outer_optimizer, warmup_steps, total_steps)
+        self._sync_time, self._sync_calls = 0, 0                       # diloco.py:23-24 (never updated)
+
+    @property
+    def avg_sync_time(self):                                            # diloco.py:62-64
+        return self._sync_time / self._sync_calls if self._sync_calls > 0 else 0
+
+    def __call__(self, *args, **kwargs):                                # diloco.py:66-67
+        return self.model(*args, **kwargs)
+
+    def train(self):
+        self.model.train()
+
+    def eval(self):
+        self.model.eval()
