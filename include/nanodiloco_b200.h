@@ -173,6 +173,15 @@ int nd_adamw(float* p, float* g, float* m, float* v, int64_t n,
              int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
              nd_stream_t stream);
 
+/* nd_adamw for a bf16 working copy (parameters and gradients bf16, moments fp32): the
+ * "bf16 inner / fp32 outer" mode of BASELINE config 2.  An extension -- the reference is fp32
+ * end to end (main.py:97-99).  Arithmetic as nd_adamw on the exactly-widened values, one rounding
+ * of the new parameter to bf16. */
+int nd_adamw_bf16(void* p_bf16, void* g_bf16, float* m, float* v, int64_t n,
+                  double lr, double beta1, double beta2, double eps, double weight_decay,
+                  int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
+                  nd_stream_t stream);
+
 /* Multi-tensor form: ptr[0]=p, ptr[1]=g, ptr[2]=m, ptr[3]=v. */
 int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
                 double lr, double beta1, double beta2, double eps, double weight_decay,

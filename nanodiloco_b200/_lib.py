@@ -40,6 +40,8 @@ SIGNATURES = {
     "nd_sumsq_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
     "nd_adamw": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
                         _c_i, _c_p]),
+    "nd_adamw_bf16": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
+                             _c_i, _c_p]),
     "nd_adamw_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f, _c_i, _c_p]),
     "nd_nccl_unique_id": (_c_i, [ctypes.c_char_p]),
     "nd_sync_ctx_create": (_c_i, [ctypes.c_char_p, _c_i, _c_i, _c_i64, _c_i, ctypes.POINTER(_c_p)]),
@@ -193,6 +195,13 @@ def adamw(p, g, m, v, *, lr: float, beta1: float = 0.9, beta2: float = 0.999, ep
           weight_decay: float = 1e-2, step: int, sumsq_dev=None, max_norm: float = 1.0,
           zero_grad: bool = False, stream=None) -> None:
     _require_cuda(p, g, m, v, sumsq_dev)
+    if _dtype_code(p) == ND_BF16:
+        if _dtype_code(g) != ND_BF16:
+            raise NDError("a bf16 working copy needs bf16 gradients")
+        check(load().nd_adamw_bf16(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), lr, beta1, beta2, eps,
+                                   weight_decay, int(step), _ptr(sumsq_dev), max_norm, int(zero_grad),
+                                   _stream(stream)), "nd_adamw_bf16")
+        return
     check(load().nd_adamw(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), lr, beta1, beta2, eps, weight_decay,
                           int(step), _ptr(sumsq_dev), max_norm, int(zero_grad), _stream(stream)), "nd_adamw")
 

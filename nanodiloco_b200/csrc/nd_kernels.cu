@@ -235,16 +235,21 @@ struct AdamHyper {
     int has_decay, zero_grad;
 };
 
-struct AdamWOp {
+// BF16: parameters and gradients are bf16 (the "bf16 inner / fp32 outer" working copy of BASELINE
+// config 2 -- an extension, the reference is fp32 end to end); moments stay fp32 and all arithmetic
+// is fp32 on the exactly-widened values, with one rounding of the new parameter back to bf16.
+template <bool BF16>
+struct AdamWOpT {
     static constexpr bool kHasSum = false;
-    float* p; float* g; float* m; float* v;
+    using PG = typename Local<BF16>::T;
+    PG* p; PG* g; float* m; float* v;
     const float* sumsq;  // nullable
     AdamHyper h;
     float coef;
     struct Regs { float4 p, g, m, v; };
 
     __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
-        p = static_cast<float*>(d.ptr[0]) + off; g = static_cast<float*>(d.ptr[1]) + off;
+        p = static_cast<PG*>(d.ptr[0]) + off; g = static_cast<PG*>(d.ptr[1]) + off;
         m = static_cast<float*>(d.ptr[2]) + off; v = static_cast<float*>(d.ptr[3]) + off;
     }
     // clip_grad.py:165-168, evaluated on the device so the host never waits for the norm
@@ -256,11 +261,11 @@ struct AdamWOp {
         }
     }
     __device__ __forceinline__ bool aligned() const {
-        return ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g) |
-                 reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0;
+        return ((reinterpret_cast<uintptr_t>(m) | reinterpret_cast<uintptr_t>(v)) & 15) == 0 &&
+               ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g)) & (BF16 ? 7 : 15)) == 0;
     }
     __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
-        r.p = ld_stream(p + i); r.g = ld_stream(g + i);
+        r.p = Local<BF16>::ld4(p, i); r.g = Local<BF16>::ld4(g, i);
         r.m = ld_stream(m + i); r.v = ld_stream(v + i);
     }
     __device__ __forceinline__ void one(float& pi, float gi, float& mi, float& vi) const {
@@ -277,16 +282,17 @@ struct AdamWOp {
         one(r.p.z, r.g.z, r.m.z, r.v.z); one(r.p.w, r.g.w, r.m.w, r.v.w);
     }
     __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
-        st_stream(p + i, r.p); st_stream(m + i, r.m); st_stream(v + i, r.v);
-        if (h.zero_grad) st_stream(g + i, make_float4(0.f, 0.f, 0.f, 0.f));
+        Local<BF16>::st4(p, i, r.p); st_stream(m + i, r.m); st_stream(v + i, r.v);
+        if (h.zero_grad) Local<BF16>::st4(g, i, make_float4(0.f, 0.f, 0.f, 0.f));
     }
     __device__ __forceinline__ void scalar(int64_t i) const {
-        float pi = p[i], mi = m[i], vi = v[i];
-        one(pi, g[i], mi, vi);
-        p[i] = pi; m[i] = mi; v[i] = vi;
-        if (h.zero_grad) g[i] = 0.0f;
+        float pi = Local<BF16>::ld1(p, i), mi = m[i], vi = v[i];
+        one(pi, Local<BF16>::ld1(g, i), mi, vi);
+        Local<BF16>::st1(p, i, pi); m[i] = mi; v[i] = vi;
+        if (h.zero_grad) Local<BF16>::st1(g, i, 0.0f);
     }
 };
+using AdamWOp = AdamWOpT<false>;
 
 template <class Op, class = void>
 struct HasPrologue { static constexpr bool value = false; };
@@ -410,40 +416,49 @@ struct ShardTileOp {
 };
 
 // buffers: 0 = p, 1 = g (zeroed in place when zero_grad), 2 = exp_avg, 3 = exp_avg_sq
-struct AdamTileOp {
+template <bool BF16>
+struct AdamTileOpT {
     static constexpr int kBufs = 4;
     static constexpr bool kHasSum = false;
-    static constexpr int kGran = 4;
-    AdamWOp o;
+    static constexpr int kEsz = BF16 ? 2 : 4;
+    static constexpr int kGran = 16 / kEsz;
+    AdamWOpT<BF16> o;
     __device__ __forceinline__ void prologue() { o.prologue(); }
     __device__ __forceinline__ float acc() const { return 0.0f; }
-    __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * 16u; }
+    __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * (8u + 2u * kEsz); }
     template <int TILE>
     __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
-        tma::bulk_load(st.buf(0), o.p + off, (uint32_t)len * 4, bar);
-        tma::bulk_load(st.buf(1), o.g + off, (uint32_t)len * 4, bar);
+        tma::bulk_load(st.buf(0), o.p + off, (uint32_t)len * kEsz, bar);
+        tma::bulk_load(st.buf(1), o.g + off, (uint32_t)len * kEsz, bar);
         tma::bulk_load(st.buf(2), o.m + off, (uint32_t)len * 4, bar);
         tma::bulk_load(st.buf(3), o.v + off, (uint32_t)len * 4, bar);
     }
     template <int TILE>
     __device__ __forceinline__ void compute(const tma::Stage<TILE>& st, int len, int tid, int nthreads) {
         for (int i = tid * 4; i < len; i += nthreads * 4) {
-            float4 p = lds4(st.buf(0) + i), g = lds4(st.buf(1) + i), m = lds4(st.buf(2) + i), v = lds4(st.buf(3) + i);
+            float4 p = BF16 ? lds_bf16x4(st.buf(0), i) : lds4(st.buf(0) + i);
+            float4 g = BF16 ? lds_bf16x4(st.buf(1), i) : lds4(st.buf(1) + i);
+            float4 m = lds4(st.buf(2) + i), v = lds4(st.buf(3) + i);
             o.one(p.x, g.x, m.x, v.x); o.one(p.y, g.y, m.y, v.y);
             o.one(p.z, g.z, m.z, v.z); o.one(p.w, g.w, m.w, v.w);
-            sts4(st.buf(0) + i, p); sts4(st.buf(2) + i, m); sts4(st.buf(3) + i, v);
-            if (o.h.zero_grad) sts4(st.buf(1) + i, make_float4(0.f, 0.f, 0.f, 0.f));
+            if (BF16) sts_bf16x4(st.buf(0), i, p); else sts4(st.buf(0) + i, p);
+            sts4(st.buf(2) + i, m); sts4(st.buf(3) + i, v);
+            if (o.h.zero_grad) {
+                if (BF16) sts_bf16x4(st.buf(1), i, make_float4(0.f, 0.f, 0.f, 0.f));
+                else sts4(st.buf(1) + i, make_float4(0.f, 0.f, 0.f, 0.f));
+            }
         }
     }
     template <int TILE>
     __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
-        tma::bulk_store(o.p + off, st.buf(0), (uint32_t)len * 4);
+        tma::bulk_store(o.p + off, st.buf(0), (uint32_t)len * kEsz);
         tma::bulk_store(o.m + off, st.buf(2), (uint32_t)len * 4);
         tma::bulk_store(o.v + off, st.buf(3), (uint32_t)len * 4);
-        if (o.h.zero_grad) tma::bulk_store(o.g + off, st.buf(1), (uint32_t)len * 4);
+        if (o.h.zero_grad) tma::bulk_store(o.g + off, st.buf(1), (uint32_t)len * kEsz);
     }
     __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
 };
+using AdamTileOp = AdamTileOpT<false>;
 
 // ===========================================================================
 // Drivers
@@ -866,6 +881,23 @@ int nd_adamw(float* p, float* g, float* m, float* v, int64_t n, double lr, doubl
     op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
     if (aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v)) {
         AdamTileOp t{op};
+        return launch_tile<ND_TILE_ADAM>(t, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
+    }
+    return launch_flat<U_ADAM, B_ADAM>(op, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int nd_adamw_bf16(void* p, void* g, float* m, float* v, int64_t n, double lr, double beta1, double beta2, double eps,
+                  double weight_decay, int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
+                  nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(n == 0 || (p && g && m && v), "null pointer");
+    ND_REQUIRE(step >= 1, "step must be >= 1 (1-based)");
+    AdamWOpT<true> op;
+    op.p = static_cast<__nv_bfloat16*>(p); op.g = static_cast<__nv_bfloat16*>(g); op.m = m; op.v = v;
+    op.sumsq = sumsq_dev; op.coef = 1.f;
+    op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+    if (aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v)) {
+        AdamTileOpT<true> t{op};
         return launch_tile<ND_TILE_ADAM>(t, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
     }
     return launch_flat<U_ADAM, B_ADAM>(op, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));

@@ -100,17 +100,25 @@ class Diloco:
         if dev.type != "cuda":
             raise _lib.NDError("nanodiloco_b200.Diloco needs CUDA parameters: the hot path is sm_100a kernels, "
                                "there is no CPU implementation")
+        # fp32 like the reference (main.py:97-99), or a bf16 working copy with fp32 master, momentum
+        # and AdamW moments ("bf16 inner / fp32 outer", BASELINE config 2 -- an extension: the
+        # reference has no such mode)
+        wdtype = self._params[0].dtype
+        if wdtype not in (torch.float32, torch.bfloat16):
+            raise ValueError(f"parameters must be float32 or bfloat16 (got {wdtype})")
         for p in self._params:
             if p.device != dev:
                 raise ValueError("all parameters must live on one device")
-            if p.dtype != torch.float32:
-                raise ValueError(f"parameters must be float32 like the reference's (got {p.dtype})")
+            if p.dtype != wdtype:
+                raise ValueError("all parameters must have one dtype")
+        self.working_dtype = wdtype
         self.device = dev
         _lib.load()
 
         # ---- flat buffers ---------------------------------------------------------------------
         W = self.world_size
-        self.layout = FlatLayout.plan(self._params, quantum=4 * W)
+        gran = 8 if wdtype == torch.bfloat16 else 4       # elements per 16 bytes of the working copy
+        self.layout = FlatLayout.plan(self._params, quantum=gran * W, align=gran)
         n = self.layout.total
         # How the W worker copies meet (W > 1):
         #   "p2p"  one fused kernel per GPU over NVLink peer memory (nd_outer_sync_p2p); needs every
@@ -122,10 +130,13 @@ class Diloco:
         self._peer = None
         if self.sync_mode == "p2p":
             from .sync import PeerContext
-            self._peer = PeerContext(W, self.rank, n, group=process_group, device=dev)
-            self._local = self._peer.local(torch.float32)[:n]
+            self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
+                                     device=dev)
+            self._local = self._peer.local(wdtype)[:n]
         else:
-            self._local = torch.zeros(n, dtype=torch.float32, device=dev)
+            if self.sync_mode == "nccl" and wdtype != torch.float32:
+                raise NotImplementedError("the NCCL pipeline handles an fp32 working copy; use sync='p2p'")
+            self._local = torch.zeros(n, dtype=wdtype, device=dev)
         rehome_(self._params, self._local, self.layout)
 
         # diloco.py:21-22: every worker starts from rank 0's parameters (one flat broadcast
@@ -146,17 +157,17 @@ class Diloco:
             from .sync import SyncContext
             lo, hi = self._peer.shard_range() if self._peer is not None else (0, n)
             self._master = torch.empty(hi - lo, dtype=torch.float32, pin_memory=True)
-            self._master.copy_(self._local[lo:hi])
-            self._off_chunk = max(4, min(int(offload_chunk_mb * (1 << 20)) // 4, hi - lo) // 4 * 4)
+            self._master.copy_(self._local[lo:hi].float())
+            self._off_chunk = max(8, min(int(offload_chunk_mb * (1 << 20)) // 4, hi - lo) // 8 * 8)
             self._off_ctx = None
             if self._peer is None:
                 self._off_ctx = SyncContext(1, 0, bucket_elems=self._off_chunk, n_streams=3, device=dev)
             self._staging = torch.empty(3 * self._off_chunk, dtype=torch.float32, device=dev)
         elif self._peer is not None:
             lo, hi = self._peer.shard_range()
-            self._master = self._local[lo:hi].clone()       # this rank's shard only: no replica
+            self._master = self._local[lo:hi].float().clone()   # this rank's shard only: no replica
         else:
-            self._master = self._local.clone()
+            self._master = self._local.float().clone()
 
         # ---- sharded sync context -------------------------------------------------------------
         self._ctx = None
@@ -178,7 +189,7 @@ class Diloco:
         self._grad = None
         self._inner_step_count = 0
         if fused_inner:
-            self._grad = torch.zeros(n, dtype=torch.float32, device=dev)
+            self._grad = torch.zeros(n, dtype=wdtype, device=dev)
             self._exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
             self._exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
             self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
@@ -272,7 +283,8 @@ class Diloco:
             kw = dict(lr=float(g["lr"]), momentum=float(g["momentum"]), dampening=float(g["dampening"]),
                       weight_decay=float(g["weight_decay"]), nesterov=bool(g["nesterov"]), first_step=first)
             if self._peer is not None:
-                self._peer.outer_sync_offloaded(self._master, self._staging, self._off_chunk, self._mom, **kw)
+                self._peer.outer_sync_offloaded(self._master, self._staging, self._off_chunk, self._mom,
+                                                dtype=self.working_dtype, **kw)
             else:
                 self._off_ctx.outer_step_offloaded(self._master, self._staging, self._off_chunk, self._mom,
                                                    self._local, **kw)
@@ -281,7 +293,8 @@ class Diloco:
                 raise NotImplementedError("the sharded outer sync supports a single outer param group")
             g = self._outer_ranges[0][0]
             self._check_outer_group(g)
-            self._peer.outer_sync(self._master, self._mom, lr=float(g["lr"]), momentum=float(g["momentum"]),
+            self._peer.outer_sync(self._master, self._mom, dtype=self.working_dtype, lr=float(g["lr"]),
+                                  momentum=float(g["momentum"]),
                                   dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
                                   nesterov=bool(g["nesterov"]), first_step=first)
         elif self._ctx is None:

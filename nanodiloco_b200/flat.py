@@ -29,18 +29,20 @@ class FlatLayout:
     quantum: int
 
     @staticmethod
-    def plan(tensors: Sequence[torch.Tensor], quantum: int = ALIGN_ELEMS) -> "FlatLayout":
+    def plan(tensors: Sequence[torch.Tensor], quantum: int = ALIGN_ELEMS, align: int = ALIGN_ELEMS) -> "FlatLayout":
         """Lays tensors out in order; `total` is padded to a multiple of `quantum`
-        (4*world for the sharded sync, so every bucket splits into aligned slices)."""
+        (4*world for the sharded sync, so every bucket splits into aligned slices).
+        `align`: elements per 16 bytes of the narrowest buffer sharing this layout (4 for fp32,
+        8 when the working copy is bf16)."""
         offsets, numels, shapes = [], [], []
         off = 0
         for t in tensors:
-            off = _round_up(off, ALIGN_ELEMS)
+            off = _round_up(off, align)
             offsets.append(off)
             numels.append(t.numel())
             shapes.append(t.shape)
             off += t.numel()
-        q = _round_up(max(quantum, ALIGN_ELEMS), ALIGN_ELEMS)
+        q = _round_up(max(quantum, align), align)
         return FlatLayout(offsets, numels, shapes, _round_up(max(off, 1), q), q)
 
     def views(self, flat: torch.Tensor) -> List[torch.Tensor]:

@@ -130,3 +130,34 @@ def test_outer_step_offloaded_master_matches_resident(golden_dir):
             assert np.array_equal(_flat(snap).numpy(), z[f"params_r{r}"])
             mom = _flat([outer.state[p]["momentum_buffer"] for p in params])
             assert np.array_equal(host(mom), z[f"mom_r{r}"])
+
+
+def test_bf16_working_copy_wrapper():
+    """bf16 inner / fp32 outer (BASELINE config 2; an extension -- the reference is fp32 end to end).
+    Oracle: the same C restatement on the exactly-widened bf16 values; master and momentum stay fp32."""
+    from oracle import oracle as O
+    torch.manual_seed(3)
+    model = torch.nn.Sequential(torch.nn.Linear(40, 33), torch.nn.Tanh(), torch.nn.Linear(33, 5)).cuda().bfloat16()
+    inner = torch.optim.AdamW(model.parameters(), lr=1e-2)
+    outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(model, inner, outer, warmup_steps=1, total_steps=40)
+    params = list(model.parameters())
+    assert all(p.dtype == torch.bfloat16 and p.data_ptr() % 16 == 0 for p in params)
+    flat32 = lambda ts: torch.cat([t.detach().reshape(-1).float() for t in ts]).cpu().numpy()
+    master = flat32(params).copy()
+    mom = np.zeros_like(master)
+    x = torch.randn(64, 40, device="cuda", dtype=torch.bfloat16)
+    for rnd in range(2):
+        for _ in range(3):
+            d(x).float().square().mean().backward()
+            assert all(p.grad.dtype == torch.bfloat16 for p in params)
+            d.inner_step()
+        local = flat32(params)
+        assert not np.array_equal(local, master)                       # the inner steps moved the weights
+        O.outer_step(master, [local.copy()], mom, lr=0.7, momentum=0.9, first_step=(rnd == 0))
+        d.outer_step()
+        got_master = flat32(d.offloaded_last_sync_parameters)          # fp32 master, bit-exact
+        assert np.array_equal(got_master, master)
+        want16 = torch.from_numpy(master).to(torch.bfloat16).float().numpy()
+        assert np.array_equal(flat32(params), want16)                  # working copy = bf16(master)
+        assert np.array_equal(flat32([outer.state[p]["momentum_buffer"] for p in params]), mom)

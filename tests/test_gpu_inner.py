@@ -123,3 +123,25 @@ def test_adamw_multi_tensor_matches_flat():
                                        _lib._stream()))
     for (p2, m2, v2), p, m, v in zip(want, ps, ms, vs):
         assert torch.equal(p, p2) and torch.equal(m, m2) and torch.equal(v, v2)
+
+
+# ---- bf16 working copy (extension: BASELINE config 2, no reference behaviour) -----------------
+
+@pytest.mark.parametrize("n", [8, 13, 4099, 300_007])
+def test_adamw_bf16_working_copy_vs_oracle(n):
+    """bf16 parameters and gradients, fp32 moments: fp32 arithmetic on the exactly-widened values
+    (the oracle's CUDA recipe), one rounding of the new parameter to bf16."""
+    p16 = torch.from_numpy(_rand(n, 1, 0.02)).to(torch.bfloat16).cuda()
+    m_np, v_np = _rand(n, 2, 1e-3), np.abs(_rand(n, 3, 1e-6))
+    m, v = dev(m_np), dev(v_np)
+    sc, ss = _lib.scratch("cuda"), torch.zeros(1, device="cuda")
+    for step in range(1, 4):
+        g16 = torch.from_numpy(_rand(n, 10 + step, 0.05 if step % 2 else 1e-4)).to(torch.bfloat16).cuda()
+        p_np, g_np = p16.float().cpu().numpy().copy(), g16.float().cpu().numpy().copy()
+        _lib.sumsq(g16, ss, sc)
+        _lib.adamw(p16, g16, m, v, lr=4e-4, step=step, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
+        coef = O.clip_coef(float(np.sqrt(np.float32(float(ss)))), 1.0)
+        O.adamw_step(p_np, g_np, m_np, v_np, lr=4e-4, step=step, clip=coef, recipe="cuda")
+        assert np.array_equal(host(m), m_np) and np.array_equal(host(v), v_np), step
+        assert torch.equal(p16.cpu(), torch.from_numpy(p_np).to(torch.bfloat16)), step
+        assert float(g16.float().abs().max()) == 0.0

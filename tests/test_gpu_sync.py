@@ -25,6 +25,9 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
                             device_id=torch.device("cuda", rank))
     z = np.load(os.path.join(GOLDEN, f"outer_w{world}.npz"))
     model = Bag(z["init"]).cuda()
+    bf16 = mode == "p2p_bf16"
+    if bf16:                                        # extension: bf16 working copy, fp32 master/momentum
+        model = model.bfloat16()
     if rank != 0:                                   # diloco.py:21-22: rank 0's parameters win
         with torch.no_grad():
             for p in model.parameters():
@@ -36,6 +39,33 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
     d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2, sync=sync, **extra)
     assert d.sync_mode == sync
     params = list(model.parameters())
+    widen = lambda a: torch.from_numpy(a).to(torch.bfloat16).float().numpy()
+    if bf16:
+        from oracle import oracle as O
+        ok = np.array_equal(_flat(params).float().cpu().numpy(), widen(z["init"]))
+        om, ob = widen(z["init"]).copy(), np.zeros_like(z["init"])
+        for r in range(3):
+            loc, off = z[f"local_r{r}_w{rank}"], 0
+            with torch.no_grad():
+                for p in params:
+                    p.copy_(torch.from_numpy(loc[off:off + p.numel()]).reshape(p.shape))
+                    off += p.numel()
+            d.outer_step()
+            O.outer_step(om, [widen(z[f"local_r{r}_w{w}"]) for w in range(world)], ob, lr=0.7, momentum=0.9,
+                         first_step=(r == 0))
+            master = _flat(d.offloaded_last_sync_parameters).cpu().numpy()
+            d.gather_outer_state()
+            mom = _flat([outer.state[p]["momentum_buffer"] for p in params]).cpu().numpy()
+            ok &= np.array_equal(master, om) and np.array_equal(mom, ob)
+            ok &= np.array_equal(_flat(params).float().cpu().numpy(), widen(om))
+        flag = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            with open(result_path, "w") as f:
+                f.write("ok" if int(flag) == 1 else "mismatch")
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     ok = np.array_equal(_flat(params).cpu().numpy(), z["init"])
     exact = world <= 2
     for r in range(3):
@@ -74,7 +104,8 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
-@pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_offload", 64.0)])
+@pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_offload", 64.0),
+                                            ("p2p_bf16", 64.0)])
 def test_sharded_outer_sync_vs_reference(world, mode, bucket_mb):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
