@@ -192,6 +192,106 @@ def run_cpu_baseline(all_shapes, n_total: int, world: int, steps: int, warmup: i
     }
 
 
+def _extras_n1(torch, _lib, dev, n, g, local, shapes, peak):
+    """N=1 side measurements: the inner step (ours vs torch foreach) and the reference's outer step on this GPU."""
+    extras = {}
+    # (3) inner step: nd_sumsq + nd_adamw(+zero-grad) over the same flat space, 32 B/elem
+    grad = torch.empty(n, device=dev).normal_(0, 1e-3, generator=g)
+    m1, v1 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    ss, sc = torch.zeros(1, device=dev), _lib.scratch(dev)
+    Ki = 10
+
+    def inner(step_no):
+        _lib.sumsq(grad, ss, sc)
+        _lib.adamw(local, grad, m1, v1, lr=4e-4, step=step_no, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
+
+    for i in range(3):
+        inner(i + 1)
+    i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    i0.record()
+    for i in range(Ki):
+        inner(i + 4)
+    i1.record()
+    torch.cuda.synchronize()
+    inner_ms = i0.elapsed_time(i1) / Ki
+    extras["inner_step"] = {"ms": inner_ms, "algorithmic_gbs": 32.0 * n / (inner_ms * 1e-3) / 1e9,
+                            "frac_of_hbm_peak": 32.0 * n / (inner_ms * 1e-3) / 1e9 / peak,
+                            "what": "nd_sumsq + nd_adamw with fused clip and zero-grad (diloco.py:57-60), "
+                                    "32 B/elem algorithmic"}
+    del grad, m1, v1
+    # the same inner step the way the reference runs it on a GPU: clip_grad_norm_ + AdamW.step()
+    # (torch foreach kernels) over the model's 201 separate tensors
+    ps = [torch.nn.Parameter(torch.empty(sh, device=dev).normal_(0, 0.02, generator=g)) for sh in shapes]
+    opt = torch.optim.AdamW(ps, lr=4e-4)
+    gs = [torch.empty_like(p_).normal_(0, 1e-3, generator=g) for p_ in ps]
+
+    def ref_inner():
+        for p_, g_ in zip(ps, gs):
+            p_.grad = g_
+        torch.nn.utils.clip_grad_norm_(ps, max_norm=1.0)
+        opt.step()
+        opt.zero_grad()
+
+    for _ in range(3):
+        ref_inner()
+    torch.cuda.synchronize()
+    i0.record()
+    for _ in range(Ki):
+        ref_inner()
+    i1.record()
+    torch.cuda.synchronize()
+    extras["inner_step"]["torch_foreach_ms"] = i0.elapsed_time(i1) / Ki
+    del opt, gs
+    # the reference's outer step on this GPU (per-tensor pageable H2D, sub, foreach SGD, clone + D2H;
+    # diloco.py:46-54) -- the path to beat on the same box
+    from oracle.torch_reference import ReferenceDilocoPort
+    inner_o = torch.optim.AdamW(ps, lr=4e-4)
+    outer_o = torch.optim.SGD(ps, lr=OUTER_LR, momentum=OUTER_MU, nesterov=True)
+    port = ReferenceDilocoPort(ps, inner_o, outer_o, 100, 10_000)
+    port.outer_step()
+    torch.cuda.synchronize()
+    t_ref = []
+    for _ in range(2):
+        t_a = time.perf_counter()
+        port.outer_step()
+        torch.cuda.synchronize()
+        t_ref.append((time.perf_counter() - t_a) * 1e3)
+    extras["reference_gpu_outer_step_ms"] = {
+        "value": min(t_ref), "what": "oracle/torch_reference.py port of the reference's outer_step run with CUDA "
+        "parameters on this GPU (host-offloaded snapshot, per-tensor copies, torch foreach SGD), wall ms, best of 2"}
+    del port, inner_o, outer_o, ps
+    torch.cuda.empty_cache()
+
+    return extras
+
+
+def _tokens_per_s(torch, dist, dev, world, args):
+    """tokens/s of the drop-in training loop (BASELINE configs[1] model size) on synthetic tokens."""
+    tokens = None
+    from nanodiloco_b200.main import train_model
+    cfg150 = {"architectures": ["LlamaForCausalLM"], "hidden_size": 1024, "intermediate_size": 2688,
+              "num_attention_heads": 16, "num_hidden_layers": 12, "rms_norm_eps": 1e-05, "use_cache": False}
+    H, rounds = args.tokens_inner_steps, 3
+    kw = dict(batch_size=8, per_device_batch_size=8, seq_length=1024, warmup_steps=10, total_steps=1000 * H,
+              inner_steps=H, max_steps=H * rounds, llama_config=cfg150)
+    st = train_model(**kw)
+    tk = torch.tensor([st["tokens_per_s_per_worker"]], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(tk, op=dist.ReduceOp.MIN)
+    tokens = {"value": float(tk) * world, "unit": "tokens/s", "per_worker_min": float(tk),
+              "outer_sync_ms": st["outer_sync_ms"], "params": st["params"],
+              "what": f"nanodiloco_b200.main.train_model, 150M-class Llama (h1024 i2688 a16 L12, fp32 like the "
+                      f"reference), per-device batch 8 x seq 1024, H={H} inner steps per outer sync ({rounds} rounds, "
+                      f"first excluded), synthetic tokens; fwd/bwd is stock HF Llama (out of scope)"}
+    if world == 1:
+        from oracle.torch_reference import ReferenceDilocoModelPort
+        st_ref = train_model(diloco_factory=ReferenceDilocoModelPort, **kw)
+        tokens["reference_port_on_gpu"] = {"value": st_ref["tokens_per_s"], "outer_sync_ms": st_ref["outer_sync_ms"]}
+
+    return tokens
+
+
 # ---------------------------------------------------------------------------------------------
 def reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
@@ -425,74 +525,11 @@ def native_arm(args):
     extras = None
     if world == 1 and not args.no_extras:
         extras = {}
-        # (3) inner step: nd_sumsq + nd_adamw(+zero-grad) over the same flat space, 32 B/elem
-        grad = torch.empty(n, device=dev).normal_(0, 1e-3, generator=g)
-        m1, v1 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
-        ss, sc = torch.zeros(1, device=dev), _lib.scratch(dev)
-        Ki = 10
-
-        def inner(step_no):
-            _lib.sumsq(grad, ss, sc)
-            _lib.adamw(local, grad, m1, v1, lr=4e-4, step=step_no, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
-
-        for i in range(3):
-            inner(i + 1)
-        i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        i0.record()
-        for i in range(Ki):
-            inner(i + 4)
-        i1.record()
-        torch.cuda.synchronize()
-        inner_ms = i0.elapsed_time(i1) / Ki
-        extras["inner_step"] = {"ms": inner_ms, "algorithmic_gbs": 32.0 * n / (inner_ms * 1e-3) / 1e9,
-                                "frac_of_hbm_peak": 32.0 * n / (inner_ms * 1e-3) / 1e9 / peak,
-                                "what": "nd_sumsq + nd_adamw with fused clip and zero-grad (diloco.py:57-60), "
-                                        "32 B/elem algorithmic"}
-        del grad, m1, v1
-        # the same inner step the way the reference runs it on a GPU: clip_grad_norm_ + AdamW.step()
-        # (torch foreach kernels) over the model's 201 separate tensors
-        ps = [torch.nn.Parameter(torch.empty(sh, device=dev).normal_(0, 0.02, generator=g)) for sh in shapes]
-        opt = torch.optim.AdamW(ps, lr=4e-4)
-        gs = [torch.empty_like(p_).normal_(0, 1e-3, generator=g) for p_ in ps]
-
-        def ref_inner():
-            for p_, g_ in zip(ps, gs):
-                p_.grad = g_
-            torch.nn.utils.clip_grad_norm_(ps, max_norm=1.0)
-            opt.step()
-            opt.zero_grad()
-
-        for _ in range(3):
-            ref_inner()
-        torch.cuda.synchronize()
-        i0.record()
-        for _ in range(Ki):
-            ref_inner()
-        i1.record()
-        torch.cuda.synchronize()
-        extras["inner_step"]["torch_foreach_ms"] = i0.elapsed_time(i1) / Ki
-        del opt, gs
-        # the reference's outer step on this GPU (per-tensor pageable H2D, sub, foreach SGD, clone + D2H;
-        # diloco.py:46-54) -- the path to beat on the same box
-        from oracle.torch_reference import ReferenceDilocoPort
-        inner_o = torch.optim.AdamW(ps, lr=4e-4)
-        outer_o = torch.optim.SGD(ps, lr=OUTER_LR, momentum=OUTER_MU, nesterov=True)
-        port = ReferenceDilocoPort(ps, inner_o, outer_o, 100, 10_000)
-        port.outer_step()
-        torch.cuda.synchronize()
-        t_ref = []
-        for _ in range(2):
-            t_a = time.perf_counter()
-            port.outer_step()
-            torch.cuda.synchronize()
-            t_ref.append((time.perf_counter() - t_a) * 1e3)
-        extras["reference_gpu_outer_step_ms"] = {
-            "value": min(t_ref), "what": "oracle/torch_reference.py port of the reference's outer_step run with CUDA "
-            "parameters on this GPU (host-offloaded snapshot, per-tensor copies, torch foreach SGD), wall ms, best of 2"}
-        del port, inner_o, outer_o, ps
-        torch.cuda.empty_cache()
-
+        try:
+            extras = _extras_n1(torch, _lib, dev, n, g, local, shapes, peak)
+        except Exception as e:  # noqa: BLE001  (a failed side measurement must not lose the bench line)
+            extras = {"error": repr(e)}
+            torch.cuda.empty_cache()
     # ---- tokens/s: the drop-in training loop on synthetic tokens (BASELINE configs[1] model) -----
     tokens = None
     if not args.no_tokens:
@@ -501,30 +538,17 @@ def native_arm(args):
             pctx.close()
             pctx = None
         torch.cuda.empty_cache()
-        from nanodiloco_b200.main import train_model
-        cfg150 = {"architectures": ["LlamaForCausalLM"], "hidden_size": 1024, "intermediate_size": 2688,
-                  "num_attention_heads": 16, "num_hidden_layers": 12, "rms_norm_eps": 1e-05, "use_cache": False}
-        H, rounds = args.tokens_inner_steps, 3
-        kw = dict(batch_size=8, per_device_batch_size=8, seq_length=1024, warmup_steps=10, total_steps=1000 * H,
-                  inner_steps=H, max_steps=H * rounds, llama_config=cfg150)
-        st = train_model(**kw)
-        tk = torch.tensor([st["tokens_per_s_per_worker"]], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tk, op=dist.ReduceOp.MIN)
-        tokens = {"value": float(tk) * world, "unit": "tokens/s", "per_worker_min": float(tk),
-                  "outer_sync_ms": st["outer_sync_ms"], "params": st["params"],
-                  "what": f"nanodiloco_b200.main.train_model, 150M-class Llama (h1024 i2688 a16 L12, fp32 like the "
-                          f"reference), per-device batch 8 x seq 1024, H={H} inner steps per outer sync ({rounds} rounds, "
-                          f"first excluded), synthetic tokens; fwd/bwd is stock HF Llama (out of scope)"}
-        if world == 1:
-            from oracle.torch_reference import ReferenceDilocoModelPort
-            st_ref = train_model(diloco_factory=ReferenceDilocoModelPort, **kw)
-            tokens["reference_port_on_gpu"] = {"value": st_ref["tokens_per_s"], "outer_sync_ms": st_ref["outer_sync_ms"]}
-
+        try:
+            tokens = _tokens_per_s(torch, dist, dev, world, args)
+        except Exception as e:  # noqa: BLE001
+            tokens = {"error": repr(e)}
     # ---- CPU baseline (rank 0, N=1 only) --------------------------------------------------------
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 3, 1, budget_s=args.cpu_budget_s)
+        try:
+            cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 3, 1, budget_s=args.cpu_budget_s)
+        except Exception as e:  # noqa: BLE001
+            cpu_baseline = {"error": repr(e)}
 
     if mode == "p2p":
         launches_per_step = 3                                          # barrier, fused kernel, barrier
