@@ -210,3 +210,7 @@ class PeerContext:
                 dist.barrier(group=self.group)      # nobody unmaps while a peer may still touch the buffer
             _lib.load().nd_peer_ctx_destroy(self._h)
             self._h = None
+            # the buffer itself: every torch view handed out by local()/peer_view() dangles from here on
+            self._bytes = None
+            _lib.load().nd_peer_free(self._ptr)
+            self._ptr = None

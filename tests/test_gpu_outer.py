@@ -211,6 +211,32 @@ def test_full_size_properties():
     assert float(master.double().sum()) == float(local.double().sum())
 
 
+def test_more_than_2_31_elements():
+    """Maximum sizes: BASELINE's microbench goes to 2e9 elements; one step past 2^31 checks that no index
+    is 32-bit anywhere (fused TMA kernel, pseudo-gradient, sum of squares)."""
+    n = (1 << 31) + 4100
+    master = torch.full((n,), 0.5, device="cuda")
+    local = torch.full((n,), 0.25, device="cuda")
+    local[-3:] = 0.0                                    # make the far end distinguishable
+    mom = torch.zeros(n, device="cuda")
+    _lib.outer_fused(master, mom, [local], lr=LR, momentum=MU, first_step=True)
+    # g = 0.25 (0.5 at the end); b = g; p = 0.5 - 0.7*(g + 0.9 g)
+    want_body, want_end = 0.5 - 0.7 * (0.25 + 0.9 * 0.25), 0.5 - 0.7 * (0.5 + 0.9 * 0.5)
+    assert torch.equal(master, local)
+    assert float(master[0]) == pytest.approx(want_body, rel=1e-6) and float(master[-1]) == pytest.approx(want_end, rel=1e-6)
+    assert float(master[(1 << 31) + 5]) == pytest.approx(want_body, rel=1e-6)
+    assert float(mom[-1]) == 0.5 and float(mom[1 << 31]) == 0.25
+    assert int((master == master[0]).sum()) == n - 3    # every element was visited exactly as expected
+    pg = torch.empty(n, device="cuda")
+    local.fill_(0.125)
+    _lib.pseudo_grad(master, local, pg)
+    assert torch.equal(pg, master - 0.125)
+    del pg, mom
+    ss, sc = torch.zeros(1, device="cuda"), _lib.scratch("cuda")
+    _lib.sumsq(local, ss, sc)
+    assert float(ss) == pytest.approx(n * 0.125 ** 2, rel=1e-6)
+
+
 # ---- peer-memory entry point on one GPU (world size 1: plumbing of the shared buffer) ------------
 
 def test_peer_context_world1_matches_oracle():
