@@ -119,6 +119,18 @@ int nd_outer_fused(float* master, float* mom, void* const* locals_host, int W,
                    int nesterov, int first_step,
                    float* sumsq_out, void* scratch, nd_stream_t stream);
 
+/* nd_outer_fused with separate READ and WRITE sets: the average runs over the W copies in
+ * `reads_host` (one per DiLoCo worker) and the new parameters are written to the `n_writes` copies
+ * in `writes_host` (every replica of every worker).  For workers that span several GPUs
+ * (BASELINE config 5: 4 workers x 2 GPUs -- the reference has no intra-worker parallelism, so
+ * this is an extension): replicas of one worker hold identical parameters, so reading one of
+ * them and writing all of them is the same outer step.  n_writes may be 0 (update master and
+ * momentum only). */
+int nd_outer_fused_rw(float* master, float* mom, void* const* reads_host, int W,
+                      void* const* writes_host, int n_writes, int local_dtype, int64_t n,
+                      float lr, float mu, float dampening, float wd, int nesterov, int first_step,
+                      float* sumsq_out, void* scratch, nd_stream_t stream);
+
 /* Multi-tensor form of nd_outer_fused for W=1:
  * ptr[0]=master, ptr[1]=mom, ptr[2]=local.  Replaces diloco.py:46-54. */
 int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
@@ -274,6 +286,11 @@ int nd_peer_ctx_create(int world, int rank, void* my_buffer, size_t bytes, const
 int nd_peer_ctx_destroy(nd_peer_ctx* ctx);
 /* Address, in this process, of rank w's buffer. */
 int nd_peer_buffer(const nd_peer_ctx* ctx, int w, void** out);
+/* Workers that span several GPUs: ranks [k*replicas, (k+1)*replicas) hold identical copies of
+ * worker k (they all-reduce their gradients every inner step).  The outer sync then averages over
+ * world/replicas workers (reading each worker's first replica) and writes every rank's copy.
+ * Default 1.  `replicas` must divide the world size.  (Extension: BASELINE config 5.) */
+int nd_peer_set_replicas(nd_peer_ctx* ctx, int replicas);
 /* Device-side barrier over the ranks (flag exchange in peer memory), enqueued on `stream`.
  * Every rank must enqueue the same sequence of barriers. */
 int nd_peer_barrier(nd_peer_ctx* ctx, nd_stream_t stream);

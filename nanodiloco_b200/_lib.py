@@ -34,6 +34,8 @@ SIGNATURES = {
                                  _c_i, _c_i, _c_p, _c_p, _c_p]),
     "nd_outer_fused": (_c_i, [_c_p, _c_p, ctypes.POINTER(_c_p), _c_i, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f,
                               _c_i, _c_i, _c_p, _c_p, _c_p]),
+    "nd_outer_fused_rw": (_c_i, [_c_p, _c_p, ctypes.POINTER(_c_p), _c_i, ctypes.POINTER(_c_p), _c_i, _c_i, _c_i64,
+                                 _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p, _c_p, _c_p]),
     "nd_outer_fused_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p]),
     "nd_sumsq": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
     "nd_sumsq_static": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p]),
@@ -58,6 +60,7 @@ SIGNATURES = {
     "nd_peer_ctx_create": (_c_i, [_c_i, _c_i, _c_p, ctypes.c_size_t, ctypes.c_char_p, ctypes.POINTER(_c_p)]),
     "nd_peer_ctx_destroy": (_c_i, [_c_p]),
     "nd_peer_buffer": (_c_i, [_c_p, _c_i, ctypes.POINTER(_c_p)]),
+    "nd_peer_set_replicas": (_c_i, [_c_p, _c_i]),
     "nd_peer_barrier": (_c_i, [_c_p, _c_p]),
     "nd_outer_sync_p2p": (_c_i, [_c_p, _c_p, _c_p, _c_i, _c_i64, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p, _c_p,
                                  _c_p]),
@@ -176,6 +179,18 @@ def outer_fused(master, mom, locals_: Sequence, *, lr: float, momentum: float, d
                                 master.numel() if n is None else n, lr, momentum, dampening, weight_decay,
                                 int(nesterov), int(first_step), _ptr(sumsq_out), _ptr(scratch_buf),
                                 _stream(stream)), "nd_outer_fused")
+
+
+def outer_fused_rw(master, mom, reads: Sequence, writes: Sequence, *, lr: float, momentum: float,
+                   dampening: float = 0.0, weight_decay: float = 0.0, nesterov: bool = True,
+                   first_step: bool = False, stream=None) -> None:
+    """nd_outer_fused_rw: average over `reads` (one copy per worker), write the result to `writes`."""
+    _require_cuda(master, mom, *reads, *writes)
+    ra = (_c_p * len(reads))(*[_ptr(t) for t in reads])
+    wa = (_c_p * max(1, len(writes)))(*[_ptr(t) for t in writes])
+    check(load().nd_outer_fused_rw(_ptr(master), _ptr(mom), ra, len(reads), wa, len(writes), _dtype_code(reads[0]),
+                                   master.numel(), lr, momentum, dampening, weight_decay, int(nesterov),
+                                   int(first_step), None, None, _stream(stream)), "nd_outer_fused_rw")
 
 
 def sumsq(g, out, scratch_buf, stream=None) -> None:

@@ -117,7 +117,9 @@ struct OuterFusedOp {
     static constexpr int kW = W > 0 ? W : 1;
     float* master;
     float* mom;
-    LocalPtrs locals;
+    LocalPtrs locals;  // the worker copies that are READ (one per DiLoCo worker)
+    LocalPtrs writes;  // the copies that receive the new parameters (every replica of every worker)
+    int n_writes;
     int w_rt;  // run-time W
     float world;
     OuterHyper h;
@@ -128,12 +130,15 @@ struct OuterFusedOp {
         master = static_cast<float*>(d.ptr[0]) + off;
         mom = static_cast<float*>(d.ptr[1]) + off;
         locals.p[0] = static_cast<typename Local<BF16>::T*>(d.ptr[2]) + off;
+        writes.p[0] = locals.p[0];
+        n_writes = 1;
     }
     __device__ __forceinline__ bool aligned() const {
         uintptr_t a = reinterpret_cast<uintptr_t>(master) | reinterpret_cast<uintptr_t>(mom);
         uintptr_t l = 0;
         const int w = W > 0 ? W : w_rt;
         for (int k = 0; k < w; ++k) l |= reinterpret_cast<uintptr_t>(locals.p[k]);
+        for (int k = 0; k < n_writes; ++k) l |= reinterpret_cast<uintptr_t>(writes.p[k]);
         return (a & 15) == 0 && (l & (BF16 ? 7 : 15)) == 0;
     }
     __device__ __forceinline__ void load4(int64_t i, Regs& r) const {
@@ -182,9 +187,7 @@ struct OuterFusedOp {
     __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
         st_stream(master + i, r.p);
         st_stream(mom + i, r.b);
-        const int w = W > 0 ? W : w_rt;
-#pragma unroll
-        for (int k = 0; k < w; ++k) Local<BF16>::st4(locals.p[k], i, r.p);
+        for (int k = 0; k < n_writes; ++k) Local<BF16>::st4(writes.p[k], i, r.p);
     }
     __device__ __forceinline__ void scalar(int64_t i) {
         const int w = W > 0 ? W : w_rt;
@@ -195,7 +198,7 @@ struct OuterFusedOp {
         if (SUM) acc = __fmaf_rn(g, g, acc);
         outer_update(g, p, b, h);
         master[i] = p; mom[i] = b;
-        for (int k = 0; k < w; ++k) Local<BF16>::st1(locals.p[k], i, p);
+        for (int k = 0; k < n_writes; ++k) Local<BF16>::st1(writes.p[k], i, p);
     }
 };
 
@@ -369,9 +372,8 @@ struct FusedTileOp {
     __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
         tma::bulk_store(o.master + off, st.buf(0), (uint32_t)len * 4);
         tma::bulk_store(o.mom + off, st.buf(1), (uint32_t)len * 4);
-#pragma unroll
-        for (int k = 0; k < W; ++k)
-            tma::bulk_store(static_cast<char*>(o.locals.p[k]) + off * kEsz, st.buf(BF16 ? 2 : 0), (uint32_t)len * kEsz);
+        for (int k = 0; k < o.n_writes; ++k)
+            tma::bulk_store(static_cast<char*>(o.writes.p[k]) + off * kEsz, st.buf(BF16 ? 2 : 0), (uint32_t)len * kEsz);
     }
     __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
 };
@@ -646,14 +648,16 @@ constexpr int U_ADAM = 1, B_ADAM = 2;
 #define ND_TILE_ADAM 2048, 2, 512, 2
 
 template <int W, bool BF16, bool SUM>
-static int launch_fused(float* master, float* mom, void* const* locals, int w_rt, int64_t n, const OuterHyper& h,
-                        float* sumsq_out, void* scratch, cudaStream_t s) {
+static int launch_fused(float* master, float* mom, void* const* locals, int w_rt, void* const* writes, int n_writes,
+                        int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s) {
     OuterFusedOp<W, BF16, SUM> op;
     op.master = master; op.mom = mom; op.w_rt = w_rt; op.world = (float)w_rt; op.h = h; op.acc = 0.f;
+    op.n_writes = n_writes;
     bool al = aligned16(master) && aligned16(mom);
     for (int k = 0; k < ND_MAX_WORKERS; ++k) {
         op.locals.p[k] = k < w_rt ? locals[k] : nullptr;
-        al = al && aligned16(op.locals.p[k]);
+        op.writes.p[k] = k < n_writes ? writes[k] : nullptr;
+        al = al && aligned16(op.locals.p[k]) && aligned16(op.writes.p[k]);
     }
     if constexpr (W > 0) {
         if (al) {  // TMA-staged path: every bulk copy needs 16-byte aligned addresses
@@ -665,21 +669,19 @@ static int launch_fused(float* master, float* mom, void* const* locals, int w_rt
         }
     }
     // register-staged path: unaligned buffers (scalar accesses) and run-time worker counts
-    if constexpr (W == 1) return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
-    else return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
+    return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
 }
 
 template <bool BF16, bool SUM>
-static int dispatch_fused(int W, float* master, float* mom, void* const* locals, int64_t n, const OuterHyper& h,
-                          float* sumsq_out, void* scratch, cudaStream_t s) {
+static int dispatch_fused(int W, float* master, float* mom, void* const* locals, void* const* writes, int n_writes,
+                          int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s) {
+#define ND_CASE(w) \
+    case w: return launch_fused<w, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s)
     switch (W) {
-        case 1: return launch_fused<1, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
-        case 2: return launch_fused<2, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
-        case 3: return launch_fused<3, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
-        case 4: return launch_fused<4, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
-        case 8: return launch_fused<8, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
-        default: return launch_fused<0, BF16, SUM>(master, mom, locals, W, n, h, sumsq_out, scratch, s);
+        ND_CASE(1); ND_CASE(2); ND_CASE(3); ND_CASE(4); ND_CASE(8);
+        default: return launch_fused<0, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s);
     }
+#undef ND_CASE
 }
 
 }  // namespace nd
@@ -757,24 +759,38 @@ int nd_outer_nesterov(float* master, float* mom, const float* pg_sum, void* loca
 #undef ND_SHARD
 }
 
-int nd_outer_fused(float* master, float* mom, void* const* locals_host, int W, int local_dtype, int64_t n, float lr,
-                   float mu, float dampening, float wd, int nesterov, int first_step, float* sumsq_out,
-                   void* scratch, nd_stream_t stream) {
+int nd_outer_fused_rw(float* master, float* mom, void* const* reads_host, int W, void* const* writes_host,
+                      int n_writes, int local_dtype, int64_t n, float lr, float mu, float dampening, float wd,
+                      int nesterov, int first_step, float* sumsq_out, void* scratch, nd_stream_t stream) {
     ND_REQUIRE(n >= 0, "n < 0");
     ND_REQUIRE(W >= 1 && W <= ND_MAX_WORKERS, "W out of range [1, ND_MAX_WORKERS]");
-    ND_REQUIRE(locals_host, "null locals_host");
+    ND_REQUIRE(n_writes >= 0 && n_writes <= ND_MAX_WORKERS, "n_writes out of range [0, ND_MAX_WORKERS]");
+    ND_REQUIRE(reads_host && (n_writes == 0 || writes_host), "null pointer array");
     ND_REQUIRE(n == 0 || (master && mom), "null pointer");
-    for (int k = 0; k < W; ++k) ND_REQUIRE(n == 0 || locals_host[k], "null local pointer");
+    for (int k = 0; k < W; ++k) ND_REQUIRE(n == 0 || reads_host[k], "null read pointer");
+    for (int k = 0; k < n_writes; ++k) ND_REQUIRE(n == 0 || writes_host[k], "null write pointer");
     ND_REQUIRE(local_dtype == ND_F32 || local_dtype == ND_BF16, "unknown local_dtype");
     ND_REQUIRE(!sumsq_out || scratch, "sumsq_out needs scratch");
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
     if (local_dtype == ND_BF16) {
-        return sumsq_out ? dispatch_fused<true, true>(W, master, mom, locals_host, n, h, sumsq_out, scratch, s)
-                         : dispatch_fused<true, false>(W, master, mom, locals_host, n, h, nullptr, nullptr, s);
+        return sumsq_out ? dispatch_fused<true, true>(W, master, mom, reads_host, writes_host, n_writes, n, h,
+                                                      sumsq_out, scratch, s)
+                         : dispatch_fused<true, false>(W, master, mom, reads_host, writes_host, n_writes, n, h,
+                                                       nullptr, nullptr, s);
     }
-    return sumsq_out ? dispatch_fused<false, true>(W, master, mom, locals_host, n, h, sumsq_out, scratch, s)
-                     : dispatch_fused<false, false>(W, master, mom, locals_host, n, h, nullptr, nullptr, s);
+    return sumsq_out ? dispatch_fused<false, true>(W, master, mom, reads_host, writes_host, n_writes, n, h,
+                                                   sumsq_out, scratch, s)
+                     : dispatch_fused<false, false>(W, master, mom, reads_host, writes_host, n_writes, n, h,
+                                                    nullptr, nullptr, s);
+}
+
+int nd_outer_fused(float* master, float* mom, void* const* locals_host, int W, int local_dtype, int64_t n, float lr,
+                   float mu, float dampening, float wd, int nesterov, int first_step, float* sumsq_out,
+                   void* scratch, nd_stream_t stream) {
+    // every copy that is read is also rewound (diloco.py:50)
+    return nd_outer_fused_rw(master, mom, locals_host, W, locals_host, W, local_dtype, n, lr, mu, dampening, wd,
+                             nesterov, first_step, sumsq_out, scratch, stream);
 }
 
 int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int local_dtype,
@@ -787,11 +803,11 @@ int nd_outer_fused_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t to
     OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
     if (local_dtype == ND_BF16) {
         OuterFusedOp<1, true, false> op;
-        op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f;
+        op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f; op.n_writes = 1;
         return launch_table<2, 3>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
     }
     OuterFusedOp<1, false, false> op;
-    op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f;
+    op.master = nullptr; op.mom = nullptr; op.w_rt = 1; op.world = 1.f; op.h = h; op.acc = 0.f; op.n_writes = 1;
     return launch_table<2, 3>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
 }
 

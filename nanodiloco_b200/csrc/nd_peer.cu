@@ -54,6 +54,7 @@ struct nd_peer_ctx {
     std::vector<void*> base;          // mapped base of rank w's buffer (own allocation for w == rank)
     uint32_t** flag_pages_dev = nullptr;
     uint32_t epoch = 0;
+    int replicas = 1;                 // consecutive ranks that hold identical copies of one worker
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timed = false;
     // side streams for the host-resident-master variant (created on first use)
@@ -145,6 +146,23 @@ int nd_peer_buffer(const nd_peer_ctx* c, int w, void** out) {
     return ND_OK;
 }
 
+int nd_peer_set_replicas(nd_peer_ctx* c, int replicas) {
+    if (!c) return set_error(ND_ESTATE, "nd_peer_set_replicas: null context");
+    if (replicas < 1 || c->world % replicas != 0)
+        return set_error(ND_EINVAL, "nd_peer_set_replicas: replicas must divide the world size");
+    c->replicas = replicas;
+    return ND_OK;
+}
+
+// Pointers into every copy at element offset `off`: one READ per worker (its first replica), a WRITE
+// for every rank.
+static int fill_rw(const nd_peer_ctx* c, size_t byte_off, void** reads, void** writes) {
+    const int workers = c->world / c->replicas;
+    for (int k = 0; k < workers; ++k) reads[k] = static_cast<char*>(c->base[k * c->replicas]) + byte_off;
+    for (int w = 0; w < c->world; ++w) writes[w] = static_cast<char*>(c->base[w]) + byte_off;
+    return workers;
+}
+
 int nd_peer_barrier(nd_peer_ctx* c, nd_stream_t stream) {
     if (!c) return set_error(ND_ESTATE, "nd_peer_barrier: null context");
     c->epoch += 1;
@@ -170,10 +188,10 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
     ND_CUDA(cudaEventRecord(c->t0, stream));
     int rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every worker's inner steps are done
-    void* locals[ND_MAX_WORKERS];
-    for (int w = 0; w < W; ++w) locals[w] = static_cast<char*>(c->base[w]) + (size_t)c->rank * shard * esz;
-    rc = nd_outer_fused(master_shard, mom_shard, locals, W, local_dtype, shard, lr, mu, dampening, wd, nesterov,
-                        first_step, sumsq_out, scratch, stream_);
+    void *reads[ND_MAX_WORKERS], *writes[ND_MAX_WORKERS];
+    const int workers = fill_rw(c, (size_t)c->rank * shard * esz, reads, writes);
+    rc = nd_outer_fused_rw(master_shard, mom_shard, reads, workers, writes, W, local_dtype, shard, lr, mu, dampening,
+                           wd, nesterov, first_step, sumsq_out, scratch, stream_);
     if (rc) return rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every shard of our copy has been written
     ND_CUDA(cudaEventRecord(c->t1, stream));
@@ -219,11 +237,10 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float*
         cudaStream_t s = c->streams[slot];  // stream order also keeps a slot from being reused too early
         float* m_dev = staging + (int64_t)slot * chunk_elems;
         ND_CUDA(cudaMemcpyAsync(m_dev, master_host_shard + off, (size_t)len * 4, cudaMemcpyHostToDevice, s));
-        void* locals[ND_MAX_WORKERS];
-        for (int w = 0; w < W; ++w)
-            locals[w] = static_cast<char*>(c->base[w]) + ((size_t)c->rank * shard + (size_t)off) * esz;
-        rc = nd_outer_fused(m_dev, mom_shard + off, locals, W, local_dtype, len, lr, mu, dampening, wd, nesterov,
-                            first_step, nullptr, nullptr, reinterpret_cast<nd_stream_t>(s));
+        void *reads[ND_MAX_WORKERS], *writes[ND_MAX_WORKERS];
+        const int workers = fill_rw(c, ((size_t)c->rank * shard + (size_t)off) * esz, reads, writes);
+        rc = nd_outer_fused_rw(m_dev, mom_shard + off, reads, workers, writes, W, local_dtype, len, lr, mu, dampening,
+                               wd, nesterov, first_step, nullptr, nullptr, reinterpret_cast<nd_stream_t>(s));
         if (rc) return rc;
         ND_CUDA(cudaMemcpyAsync(master_host_shard + off, m_dev, (size_t)len * 4, cudaMemcpyDeviceToHost, s));
     }

@@ -72,6 +72,7 @@ class Diloco:
         offload_master: bool = False,
         offload_chunk_mb: float = 64.0,
         sync: str = "auto",
+        replicas_per_worker: int = 1,
     ):
         # diloco.py:17-20
         self.model = model
@@ -86,6 +87,21 @@ class Diloco:
         self._pg_group = process_group
         self.world_size = dist.get_world_size(process_group) if dist.is_available() and dist.is_initialized() else 1
         self.rank = dist.get_rank(process_group) if self.world_size > 1 else 0
+        # A DiLoCo worker may span `replicas_per_worker` consecutive ranks (BASELINE config 5; not in the
+        # reference, where every rank is a worker): the replicas average their gradients every inner
+        # step and therefore hold identical parameters; the outer sync averages over the workers.
+        self.replicas = int(replicas_per_worker)
+        if self.replicas < 1 or self.world_size % self.replicas != 0:
+            raise ValueError("replicas_per_worker must divide the world size")
+        self._intra_group = None
+        if self.replicas > 1:
+            if process_group is not None:
+                raise NotImplementedError("replicas_per_worker needs the default process group")
+            for k in range(self.world_size // self.replicas):       # every rank creates every group
+                ranks = list(range(k * self.replicas, (k + 1) * self.replicas))
+                grp = dist.new_group(ranks)
+                if self.rank in ranks:
+                    self._intra_group = grp
 
         # The reference snapshots from outer_optimizer.param_groups (diloco.py:27-32) but zips the
         # snapshot against inner_optimizer.param_groups (diloco.py:40-46); both must enumerate the
@@ -127,11 +143,13 @@ class Diloco:
         if sync not in ("auto", "p2p", "nccl"):
             raise ValueError("sync must be 'auto', 'p2p' or 'nccl'")
         self.sync_mode = "none" if W == 1 else (self._pick_sync_mode(dev) if sync == "auto" else sync)
+        if self.replicas > 1 and self.sync_mode != "p2p":
+            raise NotImplementedError("replicas_per_worker > 1 needs the peer-memory sync (sync='p2p')")
         self._peer = None
         if self.sync_mode == "p2p":
             from .sync import PeerContext
             self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
-                                     device=dev)
+                                     device=dev, replicas=self.replicas)
             self._local = self._peer.local(wdtype)[:n]
         else:
             if self.sync_mode == "nccl" and wdtype != torch.float32:
@@ -347,6 +365,10 @@ class Diloco:
     def inner_step(self):
         """diloco.py:56-60: clip_grad_norm_(1.0) -> AdamW step -> scheduler step -> zero_grad."""
         if not self.fused_inner:
+            if self._intra_group is not None:
+                for p in self._params:
+                    if p.grad is not None:
+                        dist.all_reduce(p.grad, op=dist.ReduceOp.AVG, group=self._intra_group)
             torch.nn.utils.clip_grad_norm_(self.model.parameters(), max_norm=self.max_grad_norm)
             self.inner_optimizer.step()
             self.scheduler.step()
@@ -357,6 +379,9 @@ class Diloco:
         if not flat_ok:
             self._adopt_foreign_grads()
         self._inner_step_count += 1
+        if self._intra_group is not None:
+            # intra-worker data parallelism: one all-reduce of the flat gradient buffer over NVLink
+            dist.all_reduce(self._grad, op=dist.ReduceOp.AVG, group=self._intra_group)
         _lib.sumsq(self._grad, self._sumsq, self._scratch)
         for g, s, e in self._inner_ranges:
             if g.get("amsgrad", False) or g.get("maximize", False):

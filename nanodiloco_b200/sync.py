@@ -121,7 +121,8 @@ class PeerContext:
     the shared buffer: parameters re-homed into it are readable and writable by every rank's kernel.
     """
 
-    def __init__(self, world: int, rank: int, n_padded: int, *, elem_bytes: int = 4, group=None, device=None):
+    def __init__(self, world: int, rank: int, n_padded: int, *, elem_bytes: int = 4, group=None, device=None,
+                 replicas: int = 1):
         L = _lib.load()
         self.world, self.rank, self.group = world, rank, group
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
@@ -142,6 +143,9 @@ class PeerContext:
             _lib.check(L.nd_peer_ctx_create(world, rank, self._ptr, self.nbytes, blob, ctypes.byref(h)),
                        "nd_peer_ctx_create")
         self._h = h
+        self.replicas = int(replicas)
+        if self.replicas != 1:
+            _lib.check(L.nd_peer_set_replicas(self._h, self.replicas), "nd_peer_set_replicas")
         self._raw = _RawDeviceBuffer(self._ptr, self.nbytes)
         self._bytes = torch.as_tensor(self._raw, device=self.device)
 

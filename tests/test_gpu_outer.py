@@ -118,6 +118,26 @@ def test_outer_fused_unaligned_and_bf16():
     assert torch.equal(loc.cpu(), torch.from_numpy(master_np).to(torch.bfloat16))
 
 
+def test_outer_fused_separate_read_and_write_sets():
+    """Workers that span several GPUs (BASELINE config 5, an extension): average over one copy per worker,
+    rewind every replica.  Replicas 1 and 3 hold stale garbage on purpose: they must not be read."""
+    n = 50_003
+    master_np, mom_np = _rand(n, 1, 0.02), _rand(n, 2, 1e-3)
+    w0, w1 = master_np + _rand(n, 3, 1e-3), master_np + _rand(n, 4, 1e-3)
+    copies = [dev(w0), dev(_rand(n, 9, 5.0)), dev(w1), dev(_rand(n, 10, 5.0))]
+    master, mom = dev(master_np), dev(mom_np)
+    _lib.outer_fused_rw(master, mom, [copies[0], copies[2]], copies, lr=LR, momentum=MU)
+    O.outer_step(master_np, [w0, w1], mom_np, lr=LR, momentum=MU)
+    assert np.array_equal(host(master), master_np) and np.array_equal(host(mom), mom_np)
+    assert all(torch.equal(c, master) for c in copies)
+    # no write set at all: master and momentum move, the copies stay
+    before = copies[0].clone()
+    copies[0].add_(1e-3)
+    keep = copies[0].clone()
+    _lib.outer_fused_rw(master, mom, [copies[0]], [], lr=LR, momentum=MU)
+    assert torch.equal(copies[0], keep) and not torch.equal(master, before)
+
+
 # ---- (2) shard update after an external SUM ---------------------------------------------------
 
 @pytest.mark.parametrize("W", [2, 8])

@@ -36,6 +36,45 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
     outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
     sync = "p2p" if mode.startswith("p2p") else mode
     extra = dict(offload_master=True, offload_chunk_mb=0.001) if mode == "p2p_offload" else {}
+    if mode == "p2p_rep2":
+        # workers of 2 GPUs each (BASELINE config 5, an extension): world/2 workers, golden of that size
+        extra = dict(replicas_per_worker=2)
+        workers = world // 2
+        zw = np.load(os.path.join(GOLDEN, f"outer_w{workers}.npz"))
+        d = Diloco(model, inner, outer, 2, 100, sync="p2p", **extra)
+        params = list(model.parameters())
+        ok = True
+        for r in range(3):
+            loc, off = zw[f"local_r{r}_w{rank // 2}"], 0         # both replicas of a worker hold the same weights
+            with torch.no_grad():
+                for p in params:
+                    p.copy_(torch.from_numpy(loc[off:off + p.numel()]).reshape(p.shape))
+                    off += p.numel()
+            d.outer_step()
+            d.gather_outer_state()
+            got = _flat(params).cpu().numpy()
+            mom = _flat([outer.state[p]["momentum_buffer"] for p in params]).cpu().numpy()
+            if workers <= 2:      # order-free average: bit-exact against the reference
+                ok &= np.array_equal(got, zw[f"params_r{r}"]) and np.array_equal(mom, zw[f"mom_r{r}"])
+            else:
+                ok &= np.allclose(got, zw[f"params_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(zw[f"params_r{r}"]).max())
+                ok &= np.allclose(mom, zw[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(zw[f"mom_r{r}"]).max())
+        # inner step: replicas average their gradients and stay identical
+        for p in params:
+            p.grad.copy_(torch.full_like(p, 0.01 * (rank + 1)))
+        d.inner_step(); d.inner_step()
+        mine = _flat(params)
+        both = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(both, mine)
+        ok &= torch.equal(both[rank], both[rank ^ 1])
+        flag = torch.tensor([1 if ok else 0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if rank == 0:
+            with open(result_path, "w") as f:
+                f.write("ok" if int(flag) == 1 else "mismatch")
+        dist.barrier()
+        dist.destroy_process_group()
+        return
     d = Diloco(model, inner, outer, 2, 100, bucket_mb=bucket_mb, n_streams=2, sync=sync, **extra)
     assert d.sync_mode == sync
     params = list(model.parameters())
@@ -105,7 +144,7 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_offload", 64.0),
-                                            ("p2p_bf16", 64.0)])
+                                            ("p2p_bf16", 64.0), ("p2p_rep2", 64.0)])
 def test_sharded_outer_sync_vs_reference(world, mode, bucket_mb):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")

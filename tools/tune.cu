@@ -58,7 +58,8 @@ static void fused_variant(float* master, float* mom, float* local, int64_t n, in
     nd::OuterFusedOp<1, false, false> op;
     op.master = master; op.mom = mom; op.w_rt = 1; op.world = 1.f; op.acc = 0.f;
     op.h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
-    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k == 0 ? local : nullptr;
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = op.writes.p[k] = k == 0 ? local : nullptr;
+    op.n_writes = 1;
     char name[64];
     snprintf(name, sizeof name, "fused_w1 LDG U=%d B=%d", U, B);
     float ms = time_ms([&] {
@@ -103,7 +104,8 @@ static void tma_fused(float* master, float* mom, float* local, int64_t n, int sm
     nd::OuterFusedOp<1, false, false> op;
     op.master = master; op.mom = mom; op.w_rt = 1; op.world = 1.f; op.acc = 0.f;
     op.h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
-    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k == 0 ? local : nullptr;
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = op.writes.p[k] = k == 0 ? local : nullptr;
+    op.n_writes = 1;
     nd::FusedTileOp<1, false, false> t{op};
     char name[96];
     snprintf(name, sizeof name, "fused_w1 TMA tile=%dKB st=%d thr=%d cta/sm=%d", TILE * 4 / 1024, STAGES, THREADS, MINB);
@@ -128,7 +130,8 @@ static void tma_fused_w(float* master, float* mom, float** locals, int64_t n, in
     nd::OuterFusedOp<W, false, false> op;
     op.master = master; op.mom = mom; op.w_rt = W; op.world = (float)W; op.acc = 0.f;
     op.h = nd::make_outer_hyper(0.7f, 0.9f, 0.f, 0.f, 1, 0);
-    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = k < W ? locals[k] : nullptr;
+    for (int k = 0; k < ND_MAX_WORKERS; ++k) op.locals.p[k] = op.writes.p[k] = k < W ? locals[k] : nullptr;
+    op.n_writes = W;
     nd::FusedTileOp<W, false, false> t{op};
     char name[96];
     snprintf(name, sizeof name, "fused W=%d TMA tile=%dKB st=%d thr=%d cta/sm=%d", W, TILE * 4 / 1024, STAGES, THREADS, MINB);
