@@ -373,6 +373,19 @@ def native_arm(args):
 
         def step(first=False):
             pctx.outer_sync(master, mom, first_step=first, **hyper)
+    elif mode == "nvls":
+        # in-switch reduction (multimem) over torch symmetric memory; full master replica
+        from nanodiloco_b200.sync import NvlsContext
+        nctx = NvlsContext(world, rank, n, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, device=dev)
+        local = nctx.local()
+        local.copy_(master)
+        local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))
+        lo, hi = nctx.shard_range()
+        mom = torch.zeros(hi - lo, device=dev)
+        pg = None
+
+        def step(first=False):
+            nctx.outer_sync(master, mom, first_step=first, **hyper)
     else:
         local = master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)
         ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
@@ -416,6 +429,9 @@ def native_arm(args):
     # over the whole space (12 B/elem) is the largest HBM mover; time it on its own.
     if world == 1:
         kern_ms, kern_bytes, kern_name = ms, 24.0 * n, "outer_fused<W=1> (tma::tile_kernel)"
+    elif mode == "nvls":
+        kern_ms, kern_bytes = ms, (12.0 + 8.0 + 8.0 * (world - 1) / world + 16.0 / world) * n
+        kern_name = f"K1 + nvls_shard_kernel (multimem.ld_reduce / multimem.st) + master refresh, W={world}"
     elif mode == "p2p":
         # the step IS one launch of the fused kernel over this rank's shard (+ two flag barriers);
         # HBM bytes this GPU moves for it: its copy is read once and written once by the W owners
@@ -452,7 +468,7 @@ def native_arm(args):
 
     # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
     hbm_bytes = (24.0 if world == 1 else (8.0 + 16.0 / world if mode == "p2p" else 12.0 + 24.0 / world)) * n
-    nvl_bytes = 0.0 if world == 1 else 8.0 * (world - 1) / world * n
+    nvl_bytes = 0.0 if world == 1 else 8.0 * (world - 1) / world * n   # reduce-scatter + all-gather bytes (the roofline)
     step_roof = {"hbm_algorithmic_gbs": hbm_bytes / (ms * 1e-3) / 1e9,
                  "nvlink_algorithmic_gbs_per_dir": nvl_bytes / (ms * 1e-3) / 1e9,
                  "t_hbm_ms": hbm_bytes / (peak * 1e9) * 1e3, "t_nvlink_ms_at_900": nvl_bytes / 900e9 * 1e3}
@@ -490,7 +506,7 @@ def native_arm(args):
                        "streamed H2D -> fused kernel -> D2H in %.0f MiB chunks over 3 streams" % args.offload_chunk_mb}
         octx.close()
         del master_host, staging
-    elif mode == "p2p":
+    elif mode == "p2p" and not args.no_e2e:
         Ke = max(2, min(K, args.e2e_steps))
         shard = master.numel()
         chunk = max(4, min(int(args.offload_chunk_mb * (1 << 20)) // 4, shard) // 4 * 4)
@@ -550,7 +566,9 @@ def native_arm(args):
         except Exception as e:  # noqa: BLE001
             cpu_baseline = {"error": repr(e)}
 
-    if mode == "p2p":
+    if mode == "nvls":
+        launches_per_step = 4                                          # K1, barrier, NVLS kernel, barrier
+    elif mode == "p2p":
         launches_per_step = 3                                          # barrier, fused kernel, barrier
     elif world > 1:
         launches_per_step = 2 * ((n + ctx.bucket - 1) // ctx.bucket)   # K1 + K2 per bucket
@@ -566,7 +584,7 @@ def native_arm(args):
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
             "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
-            "bucket_mb": args.bucket_mb if mode == "nccl" else None, "sync": mode, "extras": extras, "tokens_per_s": tokens,
+            "bucket_mb": args.bucket_mb if mode in ("nccl", "nvls") else None, "sync": mode, "extras": extras, "tokens_per_s": tokens,
         }
         print(json.dumps(line), flush=True)
     if ctx is not None:
@@ -588,12 +606,13 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="llama1b")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--streams", type=int, default=2)
-    ap.add_argument("--sync", choices=["p2p", "nccl"], default="p2p",
+    ap.add_argument("--sync", choices=["p2p", "nccl", "nvls"], default="p2p",
                     help="N>1: fused peer-memory kernel (default) or bucketed NCCL reduce-scatter/all-gather")
     ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--cpu-budget-s", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="N>1 tuning runs: skip the host-resident-master measurement")
     ap.add_argument("--no-tokens", action="store_true", help="skip the tokens/s training-loop measurement")
     ap.add_argument("--tokens-inner-steps", type=int, default=10)
     ap.add_argument("--no-extras", action="store_true", help="skip the inner-step and reference-GPU-path timings")

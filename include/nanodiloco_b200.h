@@ -318,6 +318,31 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* ctx, float* master_host_shard, floa
                                 int64_t chunk_elems, float* mom_shard, int local_dtype,
                                 int64_t n_padded, float lr, float mu, float dampening, float wd,
                                 int nesterov, int first_step, nd_stream_t stream);
+/* A peer context over buffers the CALLER has already mapped into every rank (e.g. torch
+ * symmetric memory): bases_host[w] = address, in this process, of rank w's buffer of
+ * `bytes` payload + a 4096-byte flag page (zero-filled).  Nothing is mapped or unmapped here. */
+int nd_peer_ctx_create_from_ptrs(int world, int rank, void* const* bases_host, size_t bytes,
+                                 nd_peer_ctx** out);
+
+/* The outer step with the cross-worker sum taken INSIDE the NVSwitch (NVLS multicast):
+ *   K1  pg = master - local on every rank (whole space)            diloco.py:48
+ *   barrier
+ *   this rank's shard: g = multimem.ld_reduce.add(pg)/W (the switch sums every rank's pg),
+ *   Nesterov update of master/momentum shard, multimem.st of the new parameters into every
+ *   rank's working copy                                            diloco.py:49-52
+ *   barrier; the master replica's other shards are refreshed from the working copy (diloco.py:54)
+ * run bucket by bucket (bucket_elems, rounded up to a multiple of 4*world; rank r owns the r-th
+ * slice of every bucket, mom_shard is the concatenation of its slices) on three internal streams so
+ * that the two HBM-only passes hide under the NVLink pass of the neighbouring buckets.
+ * local, pg: this rank's two symmetric buffers (plain addresses); mc_local, mc_pg: the multicast
+ * addresses of the same two buffers; master: full fp32 replica (n_padded); mom_shard: n_padded/W.
+ * fp32 only.  The summation order inside the switch is the hardware's: results equal the
+ * reference bit for bit at W = 2 and within the stated tolerance beyond (like NCCL's or gloo's
+ * order).  Per direction and GPU ~4*(1+1/W) B/element cross NVLink instead of 8*(W-1)/W. */
+int nd_outer_sync_nvls(nd_peer_ctx* ctx, float* local, float* pg, float* mc_local, float* mc_pg,
+                       float* master, float* mom_shard, int64_t n_padded, int64_t bucket_elems,
+                       float lr, float mu, float dampening, float wd, int nesterov, int first_step,
+                       nd_stream_t stream);
 int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
 
 #ifdef __cplusplus

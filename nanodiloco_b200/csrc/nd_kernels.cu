@@ -17,6 +17,7 @@
 // kUnroll independent groups before any dependent arithmetic or store, so each
 // thread keeps kUnroll x (#inputs) 128-bit requests in flight.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 
@@ -665,7 +666,15 @@ static int launch_fused(float* master, float* mom, void* const* locals, int w_rt
             if constexpr (W == 1) return launch_tile<ND_TILE_FUSED1>(t, n, scratch, sumsq_out, s);
             else if constexpr (W == 2) return launch_tile<ND_TILE_FUSED2>(t, n, scratch, sumsq_out, s);
             else if constexpr (W <= 4) return launch_tile<ND_TILE_FUSED4>(t, n, scratch, sumsq_out, s);
-            else return launch_tile<ND_TILE_FUSED8>(t, n, scratch, sumsq_out, s);
+            else {
+                // ND_P2P8_VARIANT: alternative stage shapes for 5..8 worker copies (tuning knob)
+                static int v = -1;
+                if (v < 0) { const char* e = getenv("ND_P2P8_VARIANT"); v = e ? atoi(e) : 0; }
+                if (v == 1) return launch_tile<2048, 2, 256, 1>(t, n, scratch, sumsq_out, s);
+                if (v == 2) return launch_tile<1024, 4, 512, 1>(t, n, scratch, sumsq_out, s);
+                if (v == 3) return launch_tile<512, 3, 128, 3>(t, n, scratch, sumsq_out, s);
+                return launch_tile<ND_TILE_FUSED8>(t, n, scratch, sumsq_out, s);
+            }
         }
     }
     // register-staged path: unaligned buffers (scalar accesses) and run-time worker counts

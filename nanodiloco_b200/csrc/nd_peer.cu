@@ -14,6 +14,7 @@
 // enough.  Same wire bytes as reduce-scatter + all-gather: 8*(W-1)/W bytes per element per direction.
 //
 // Replaces nanodiloco/diloco/diloco.py:46-54 including the collective of :49.
+#include <cstdlib>
 #include <cstring>
 #include <vector>
 
@@ -27,13 +28,15 @@ constexpr size_t kFlagBytes = 4096;  // per-rank flag page appended to the share
 // Barrier across the ranks of a node: thread w publishes `epoch` to slot [rank] of rank w's flag
 // page, then waits until slot [w] of our own page reaches `epoch`.  System-scope release/acquire;
 // bounded wait (~10 s of SM clock) so that a dead peer traps this rank instead of hanging the box.
-__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int rank, uint32_t epoch) {
+__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int rank, uint32_t epoch, int channel) {
     const int w = threadIdx.x;
     if (w >= world) return;
     __threadfence_system();
-    uint32_t* remote = flag_pages[w] + rank;
+    // each channel has its own ND_MAX_WORKERS slots, so barriers issued on different streams (whose
+    // relative order on the device is not fixed) can never satisfy one another
+    uint32_t* remote = flag_pages[w] + channel * ND_MAX_WORKERS + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
-    const uint32_t* mine = flag_pages[rank] + w;
+    const uint32_t* mine = flag_pages[rank] + channel * ND_MAX_WORKERS + w;
     const long long t0 = clock64();
     for (;;) {
         uint32_t v;
@@ -42,6 +45,56 @@ __global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int 
         if (clock64() - t0 > 20000000000LL) __trap();
     }
     __threadfence_system();
+}
+
+// ---- NVLS: the cross-worker sum is taken INSIDE the NVSwitch ---------------------------------
+// multimem.ld_reduce on a multicast address returns the sum over every GPU's copy of that address
+// (SASS: LDGMC.E.ADD.F32x4); multimem.st writes every GPU's copy at once.  Per direction and GPU
+// the wire then carries ~4.5 B/element at W=8 instead of 7 for reduce-scatter + all-gather.
+__device__ __forceinline__ float4 mc_ld_reduce_add(const float* mc) {
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void mc_st(float* mc, const float4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                 :: "l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
+// This rank's shard: g = (in-switch sum of every worker's pseudo-gradient) / W, Nesterov update of
+// the master and momentum shards (local HBM), new parameters multicast into every worker's copy.
+template <int U, int MINB>
+__global__ void __launch_bounds__(kThreads, MINB) nvls_shard_kernel(float* __restrict__ master, float* __restrict__ mom,
+                                                                const float* mc_pg, float* mc_local, int64_t n,
+                                                                float world, OuterHyper h) {
+    const int64_t nvec = n >> 2;
+    const int64_t nthreads = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    auto one = [&](float& p, float& b, float s) { outer_update(__fdiv_rn(s, world), p, b, h); };
+    for (; i < nvec; i += (int64_t)U * nthreads) {
+        float4 s[U], p[U], b[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = i + u * nthreads;
+            if (j < nvec) {
+                s[u] = mc_ld_reduce_add(mc_pg + (j << 2));
+                p[u] = ld_stream(master + (j << 2));
+                b[u] = h.first_step ? make_float4(0.f, 0.f, 0.f, 0.f) : ld_stream(mom + (j << 2));
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const int64_t j = i + u * nthreads;
+            if (j < nvec) {
+                one(p[u].x, b[u].x, s[u].x); one(p[u].y, b[u].y, s[u].y);
+                one(p[u].z, b[u].z, s[u].z); one(p[u].w, b[u].w, s[u].w);
+                st_stream(master + (j << 2), p[u]);
+                st_stream(mom + (j << 2), b[u]);
+                mc_st(mc_local + (j << 2), p[u]);
+            }
+        }
+    }
 }
 
 }  // namespace nd
@@ -53,8 +106,10 @@ struct nd_peer_ctx {
     size_t bytes = 0;                 // payload bytes of each rank's buffer (flags follow)
     std::vector<void*> base;          // mapped base of rank w's buffer (own allocation for w == rank)
     uint32_t** flag_pages_dev = nullptr;
-    uint32_t epoch = 0;
+    static constexpr int kChannels = 4;
+    uint32_t epoch[kChannels] = {0, 0, 0, 0};
     int replicas = 1;                 // consecutive ranks that hold identical copies of one worker
+    bool owns_mappings = true;        // false: the peer addresses were mapped by the caller (symmetric memory)
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timed = false;
     // side streams for the host-resident-master variant (created on first use)
@@ -62,6 +117,7 @@ struct nd_peer_ctx {
     cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr};
     cudaEvent_t done[kStreams] = {nullptr, nullptr, nullptr};
     cudaEvent_t fork = nullptr;
+    std::vector<cudaEvent_t> bucket_events;  // NVLS pipeline: two per bucket
 };
 
 extern "C" {
@@ -124,15 +180,39 @@ int nd_peer_ctx_create(int world, int rank, void* my_buffer, size_t bytes, const
     return ND_OK;
 }
 
+int nd_peer_ctx_create_from_ptrs(int world, int rank, void* const* bases_host, size_t bytes, nd_peer_ctx** out) {
+    if (!out) return set_error(ND_EINVAL, "nd_peer_ctx_create_from_ptrs: null out");
+    *out = nullptr;
+    if (world < 1 || world > ND_MAX_WORKERS || rank < 0 || rank >= world)
+        return set_error(ND_EINVAL, "nd_peer_ctx_create_from_ptrs: bad world/rank (world <= ND_MAX_WORKERS)");
+    if (!bases_host || bytes == 0) return set_error(ND_EINVAL, "nd_peer_ctx_create_from_ptrs: null bases");
+    for (int w = 0; w < world; ++w)
+        if (!bases_host[w]) return set_error(ND_EINVAL, "nd_peer_ctx_create_from_ptrs: null base for rank %d", w);
+    nd_peer_ctx* c = new nd_peer_ctx();
+    c->world = world; c->rank = rank; c->bytes = (bytes + 255) / 256 * 256;
+    c->owns_mappings = false;
+    c->base.assign(bases_host, bases_host + world);
+    std::vector<uint32_t*> pages(world);
+    for (int w = 0; w < world; ++w) pages[w] = reinterpret_cast<uint32_t*>(static_cast<char*>(c->base[w]) + c->bytes);
+    ND_CUDA(cudaMalloc(&c->flag_pages_dev, sizeof(uint32_t*) * world));
+    ND_CUDA(cudaMemcpy(c->flag_pages_dev, pages.data(), sizeof(uint32_t*) * world, cudaMemcpyHostToDevice));
+    ND_CUDA(cudaEventCreate(&c->t0));
+    ND_CUDA(cudaEventCreate(&c->t1));
+    *out = c;
+    return ND_OK;
+}
+
 int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     if (!c) return ND_OK;
-    for (int w = 0; w < c->world; ++w)
-        if (w != c->rank && c->base[w]) cudaIpcCloseMemHandle(c->base[w]);
+    if (c->owns_mappings)
+        for (int w = 0; w < c->world; ++w)
+            if (w != c->rank && c->base[w]) cudaIpcCloseMemHandle(c->base[w]);
     for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
         if (c->streams[i]) cudaStreamDestroy(c->streams[i]);
         if (c->done[i]) cudaEventDestroy(c->done[i]);
     }
     if (c->fork) cudaEventDestroy(c->fork);
+    for (auto e : c->bucket_events) cudaEventDestroy(e);
     if (c->flag_pages_dev) cudaFree(c->flag_pages_dev);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
@@ -163,12 +243,15 @@ static int fill_rw(const nd_peer_ctx* c, size_t byte_off, void** reads, void** w
     return workers;
 }
 
+static int peer_barrier_ch(nd_peer_ctx* c, int channel, cudaStream_t stream) {
+    c->epoch[channel] += 1;
+    peer_barrier_kernel<<<1, 32, 0, stream>>>(c->flag_pages_dev, c->world, c->rank, c->epoch[channel], channel);
+    return check_launch("peer_barrier_kernel");
+}
+
 int nd_peer_barrier(nd_peer_ctx* c, nd_stream_t stream) {
     if (!c) return set_error(ND_ESTATE, "nd_peer_barrier: null context");
-    c->epoch += 1;
-    peer_barrier_kernel<<<1, 32, 0, reinterpret_cast<cudaStream_t>(stream)>>>(c->flag_pages_dev, c->world, c->rank,
-                                                                              c->epoch);
-    return check_launch("peer_barrier_kernel");
+    return peer_barrier_ch(c, 0, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int local_dtype, int64_t n_padded,
@@ -199,6 +282,16 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
     return ND_OK;
 }
 
+static int ensure_side_streams(nd_peer_ctx* c) {
+    if (c->fork) return ND_OK;  // first use: side streams and the events that join them to the caller's stream
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
+        ND_CUDA(cudaStreamCreateWithFlags(&c->streams[i], cudaStreamNonBlocking));
+        ND_CUDA(cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming));
+    }
+    ND_CUDA(cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming));
+    return ND_OK;
+}
+
 int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float* staging, int64_t chunk_elems,
                                 float* mom_shard, int local_dtype, int64_t n_padded, float lr, float mu,
                                 float dampening, float wd, int nesterov, int first_step, nd_stream_t stream_) {
@@ -217,16 +310,10 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float*
     if (n_padded && (!master_host_shard || !staging || !mom_shard))
         return set_error(ND_EINVAL, "nd_outer_sync_p2p_offloaded: null pointer");
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-    if (!c->fork) {  // first use: side streams and the events that join them to the caller's stream
-        for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
-            ND_CUDA(cudaStreamCreateWithFlags(&c->streams[i], cudaStreamNonBlocking));
-            ND_CUDA(cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming));
-        }
-        ND_CUDA(cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming));
-    }
+    int rc;
+    if ((rc = ensure_side_streams(c))) return rc;
     const int64_t shard = n_padded / W;
     ND_CUDA(cudaEventRecord(c->t0, stream));
-    int rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
     ND_CUDA(cudaEventRecord(c->fork, stream));
     for (int i = 0; i < nd_peer_ctx::kStreams; ++i) ND_CUDA(cudaStreamWaitEvent(c->streams[i], c->fork, 0));
@@ -249,6 +336,103 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float*
         ND_CUDA(cudaStreamWaitEvent(stream, c->done[i], 0));
     }
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
+    ND_CUDA(cudaEventRecord(c->t1, stream));
+    c->timed = true;
+    return ND_OK;
+}
+
+// In-flight depth of the in-switch loads: U independent 16-byte multimem.ld_reduce per thread, MINB
+// resident CTAs of 512 threads per SM.  ND_NVLS_VARIANT (0..3) selects among the compiled shapes.
+static int nvls_variant() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("ND_NVLS_VARIANT");
+        v = e ? atoi(e) : 0;
+        if (v < 0 || v > 3) v = 0;
+    }
+    return v;
+}
+
+static int nvls_launch(nd_peer_ctx* c, float* master, float* mom, const float* mc_pg, float* mc_local, int64_t n,
+                       const OuterHyper& h, cudaStream_t stream) {
+    if (n <= 0) return ND_OK;
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int64_t need = ((n >> 2) + kThreads - 1) / kThreads;
+    auto grid_for = [&](int minb) {
+        return (int)(need < (int64_t)sms * minb ? (need > 0 ? need : 1) : (int64_t)sms * minb);
+    };
+    const float w = (float)c->world;
+    switch (nvls_variant()) {
+        case 1: nvls_shard_kernel<4, 2><<<grid_for(2), kThreads, 0, stream>>>(master, mom, mc_pg, mc_local, n, w, h); break;
+        case 2: nvls_shard_kernel<2, 4><<<grid_for(4), kThreads, 0, stream>>>(master, mom, mc_pg, mc_local, n, w, h); break;
+        case 3: nvls_shard_kernel<8, 1><<<grid_for(1), kThreads, 0, stream>>>(master, mom, mc_pg, mc_local, n, w, h); break;
+        default: nvls_shard_kernel<2, 2><<<grid_for(2), kThreads, 0, stream>>>(master, mom, mc_pg, mc_local, n, w, h); break;
+    }
+    return check_launch("nvls_shard_kernel");
+}
+
+int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local, float* mc_pg, float* master,
+                       float* mom_shard, int64_t n_padded, int64_t bucket_elems, float lr, float mu, float dampening,
+                       float wd, int nesterov, int first_step, nd_stream_t stream_) {
+    if (!c) return set_error(ND_ESTATE, "nd_outer_sync_nvls: null context");
+    const int W = c->world;
+    if (c->replicas != 1) return set_error(ND_ESTATE, "nd_outer_sync_nvls: replicas are not supported");
+    const int64_t q = 4 * (int64_t)W;
+    if (n_padded < 0 || n_padded % q != 0)
+        return set_error(ND_EINVAL, "nd_outer_sync_nvls: n_padded must be a multiple of 4*world");
+    if ((size_t)n_padded * 4 > c->bytes) return set_error(ND_EINVAL, "nd_outer_sync_nvls: n_padded exceeds the buffers");
+    if (n_padded && (!local || !pg || !mc_local || !mc_pg || !master || !mom_shard))
+        return set_error(ND_EINVAL, "nd_outer_sync_nvls: null pointer");
+    if (bucket_elems < 1) return set_error(ND_EINVAL, "nd_outer_sync_nvls: bucket_elems < 1");
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    const int64_t bucket = (bucket_elems + q - 1) / q * q;
+    const int64_t nb = (n_padded + bucket - 1) / bucket;
+    const OuterHyper h{-lr, mu, 1.0f - dampening, wd, nesterov, first_step};
+    int rc;
+    if ((rc = ensure_side_streams(c))) return rc;
+    // Three lanes, bucket by bucket (bucket b = [b*B, min((b+1)*B, n)); rank r owns its r-th slice):
+    //   lane A  K1: pg_b = master_b - local_b                                   (HBM)
+    //   lane B  barrier(all ranks' pg_b are in memory) -> in-switch sum + update + multicast store   (NVLink)
+    //   lane C  barrier(every copy of bucket b is written) -> master replica refresh of bucket b       (HBM)
+    // so the HBM-only passes of buckets b+1 and b-1 hide under the NVLink pass of bucket b.
+    cudaStream_t sa = c->streams[0], sb = c->streams[1], sc = c->streams[2];
+    ND_CUDA(cudaEventRecord(c->t0, stream));
+    ND_CUDA(cudaEventRecord(c->fork, stream));
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) ND_CUDA(cudaStreamWaitEvent(c->streams[i], c->fork, 0));
+    if ((int64_t)c->bucket_events.size() < 2 * nb) {
+        const size_t old = c->bucket_events.size();
+        c->bucket_events.resize(2 * nb);
+        for (size_t i = old; i < c->bucket_events.size(); ++i)
+            ND_CUDA(cudaEventCreateWithFlags(&c->bucket_events[i], cudaEventDisableTiming));
+    }
+    for (int64_t b = 0; b < nb; ++b) {
+        const int64_t off = b * bucket;
+        const int64_t len = (n_padded - off < bucket) ? (n_padded - off) : bucket;
+        const int64_t slice = len / W, mine = off + (int64_t)c->rank * slice;
+        const int64_t shard_off = b * (bucket / W);
+        cudaEvent_t k1_done = c->bucket_events[2 * b], upd_done = c->bucket_events[2 * b + 1];
+        if ((rc = nd_pseudo_grad(master + off, local + off, ND_F32, pg + off, len, reinterpret_cast<nd_stream_t>(sa))))
+            return rc;
+        ND_CUDA(cudaEventRecord(k1_done, sa));
+        ND_CUDA(cudaStreamWaitEvent(sb, k1_done, 0));
+        if ((rc = peer_barrier_ch(c, 1, sb))) return rc;
+        if ((rc = nvls_launch(c, master + mine, mom_shard + shard_off, mc_pg + mine, mc_local + mine, slice, h, sb)))
+            return rc;
+        ND_CUDA(cudaEventRecord(upd_done, sb));
+        ND_CUDA(cudaStreamWaitEvent(sc, upd_done, 0));
+        if ((rc = peer_barrier_ch(c, 2, sc))) return rc;
+        // theta_sync replica: the slices other ranks own are refreshed from the working copy (diloco.py:54)
+        if (mine > off)
+            ND_CUDA(cudaMemcpyAsync(master + off, local + off, (size_t)(mine - off) * 4, cudaMemcpyDeviceToDevice, sc));
+        if (mine + slice < off + len)
+            ND_CUDA(cudaMemcpyAsync(master + mine + slice, local + mine + slice,
+                                    (size_t)(off + len - mine - slice) * 4, cudaMemcpyDeviceToDevice, sc));
+    }
+    for (int i = 0; i < nd_peer_ctx::kStreams; ++i) {
+        ND_CUDA(cudaEventRecord(c->done[i], c->streams[i]));
+        ND_CUDA(cudaStreamWaitEvent(stream, c->done[i], 0));
+    }
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
     return ND_OK;

@@ -140,13 +140,24 @@ class Diloco:
         #   "p2p"  one fused kernel per GPU over NVLink peer memory (nd_outer_sync_p2p); needs every
         #          rank on one node with peer access.  Master and momentum are sharded 1/W.
         #   "nccl" bucketed reduce-scatter -> shard update -> all-gather (nd_outer_sync).
-        if sync not in ("auto", "p2p", "nccl"):
-            raise ValueError("sync must be 'auto', 'p2p' or 'nccl'")
+        #   "nvls" in-switch reduction (multimem.ld_reduce / multimem.st over symmetric memory,
+        #          nd_outer_sync_nvls): fewest NVLink bytes; full master replica; fp32; the sum order
+        #          is the switch's, so W > 2 matches the reference within tolerance, not bit for bit.
+        if sync not in ("auto", "p2p", "nccl", "nvls"):
+            raise ValueError("sync must be 'auto', 'p2p', 'nccl' or 'nvls'")
         self.sync_mode = "none" if W == 1 else (self._pick_sync_mode(dev) if sync == "auto" else sync)
-        if self.replicas > 1 and self.sync_mode != "p2p":
+        if self.replicas > 1 and self.sync_mode != "p2p":  # (nvls: checked below)
             raise NotImplementedError("replicas_per_worker > 1 needs the peer-memory sync (sync='p2p')")
         self._peer = None
-        if self.sync_mode == "p2p":
+        self._nvls = None
+        if self.sync_mode == "nvls":
+            if wdtype != torch.float32 or offload_master or self.replicas > 1:
+                raise NotImplementedError("sync='nvls' handles an fp32 working copy, resident master, one rank per worker")
+            from .sync import NvlsContext
+            self._nvls = NvlsContext(W, self.rank, n, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
+                                     group=process_group, device=dev)
+            self._local = self._nvls.local()
+        elif self.sync_mode == "p2p":
             from .sync import PeerContext
             self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
                                      device=dev, replicas=self.replicas)
@@ -189,8 +200,8 @@ class Diloco:
 
         # ---- sharded sync context -------------------------------------------------------------
         self._ctx = None
-        if self._peer is not None:
-            lo, hi = self._peer.shard_range()
+        if self._peer is not None or self._nvls is not None:
+            lo, hi = (self._peer or self._nvls).shard_range()
             self._mom = torch.zeros(hi - lo, dtype=torch.float32, device=dev)
             self._pg = None
         elif W > 1:
@@ -306,6 +317,14 @@ class Diloco:
             else:
                 self._off_ctx.outer_step_offloaded(self._master, self._staging, self._off_chunk, self._mom,
                                                    self._local, **kw)
+        elif self._nvls is not None:
+            if len(self._outer_ranges) != 1:
+                raise NotImplementedError("the sharded outer sync supports a single outer param group")
+            g = self._outer_ranges[0][0]
+            self._check_outer_group(g)
+            self._nvls.outer_sync(self._master, self._mom, lr=float(g["lr"]), momentum=float(g["momentum"]),
+                                  dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
+                                  nesterov=bool(g["nesterov"]), first_step=first)
         elif self._peer is not None:
             if len(self._outer_ranges) != 1:
                 raise NotImplementedError("the sharded outer sync supports a single outer param group")
@@ -345,16 +364,18 @@ class Diloco:
     def _publish_outer_state(self) -> None:
         """outer_optimizer.state[p]['momentum_buffer'] as views (world size 1).  With the
         sharded sync each rank holds 1/W of the momentum; `gather_outer_state()` assembles it."""
-        if self._ctx is not None or self._peer is not None:
+        if self._ctx is not None or self._peer is not None or self._nvls is not None:
             return
         for p, v in zip(self._params, self.layout.views(self._mom)):
             self.outer_optimizer.state[p]["momentum_buffer"] = v
 
     def gather_outer_state(self) -> None:
         """Collective: materialise the full momentum buffers into outer_optimizer.state."""
-        if self._ctx is None and self._peer is None:
+        if self._ctx is None and self._peer is None and self._nvls is None:
             return self._publish_outer_state()
-        if self._peer is not None:
+        if self._nvls is not None:
+            full = self._nvls.gather_shards(self._mom)
+        elif self._peer is not None:
             full = self._peer.gather_shards(self._mom)
         else:
             full = self._ctx.gather_shards(self._mom, self.layout.total)

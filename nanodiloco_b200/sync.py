@@ -218,3 +218,84 @@ class PeerContext:
             self._bytes = None
             _lib.load().nd_peer_free(self._ptr)
             self._ptr = None
+
+
+class NvlsContext:
+    """Host side of `nd_outer_sync_nvls`: the cross-worker sum is taken inside the NVSwitch.
+
+    Needs two buffers that every rank maps AND that have a multicast address: the working
+    parameters and the pseudo-gradient staging.  They come from torch's symmetric memory
+    (`torch.distributed._symmetric_memory`: CUDA VMM allocations bound to a multicast object) --
+    plumbing, like the process group itself; the kernels that use the multicast addresses are ours.
+    """
+
+    def __init__(self, world: int, rank: int, n_padded: int, *, bucket_elems: int = 1 << 25, group=None,
+                 device=None):
+        import torch.distributed._symmetric_memory as symm
+        q = 4 * world
+        self.bucket = (int(bucket_elems) + q - 1) // q * q
+        L = _lib.load()
+        self.world, self.rank, self.group = world, rank, group
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.n_padded = int(n_padded)
+        payload = (self.n_padded * 4 + 255) // 256 * 256
+        gname = (group if group is not None else dist.group.WORLD).group_name
+        with torch.cuda.device(self.device):
+            self._buf_local = symm.empty(payload + 4096, dtype=torch.uint8, device=self.device)
+            self._buf_pg = symm.empty(payload, dtype=torch.uint8, device=self.device)
+            self._buf_local.zero_()
+            self._buf_pg.zero_()
+            h_local = symm.rendezvous(self._buf_local, gname)
+            h_pg = symm.rendezvous(self._buf_pg, gname)
+            if not h_local.multicast_ptr or not h_pg.multicast_ptr:
+                raise _lib.NDError("this system offers no NVLS multicast address for symmetric memory; use sync='p2p'")
+            self._handles = (h_local, h_pg)
+            self.mc_local, self.mc_pg = int(h_local.multicast_ptr), int(h_pg.multicast_ptr)
+            bases = (ctypes.c_void_p * world)(*[int(p) for p in h_local.buffer_ptrs])
+            h = ctypes.c_void_p()
+            _lib.check(L.nd_peer_ctx_create_from_ptrs(world, rank, bases, payload, ctypes.byref(h)),
+                       "nd_peer_ctx_create_from_ptrs")
+            torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)           # every rank's flag page is zero before anyone signals
+        self._h = h
+
+    def local(self) -> torch.Tensor:
+        return self._buf_local[: self.n_padded * 4].view(torch.float32)
+
+    def pg(self) -> torch.Tensor:
+        return self._buf_pg[: self.n_padded * 4].view(torch.float32)
+
+    def shard_range(self, rank=None):
+        r = self.rank if rank is None else rank
+        s = self.n_padded // self.world
+        return r * s, (r + 1) * s
+
+    def outer_sync(self, master, mom_shard, *, lr, momentum, dampening=0.0, weight_decay=0.0, nesterov=True,
+                   first_step=False, stream=None) -> None:
+        _lib._require_cuda(master, mom_shard)
+        _lib.check(_lib.load().nd_outer_sync_nvls(
+            self._h, self.local().data_ptr(), self.pg().data_ptr(), self.mc_local, self.mc_pg, _lib._ptr(master),
+            _lib._ptr(mom_shard), self.n_padded, self.bucket, lr, momentum, dampening, weight_decay, int(nesterov),
+            int(first_step), _lib._stream(stream)), "nd_outer_sync_nvls")
+
+    def last_ms(self) -> float:
+        ms = ctypes.c_float()
+        _lib.check(_lib.load().nd_peer_last_ms(self._h, ctypes.byref(ms)), "nd_peer_last_ms")
+        return float(ms.value)
+
+    def gather_shards(self, shard: torch.Tensor) -> torch.Tensor:
+        """Collective: bucket-interleaved shards (rank r owns the r-th slice of every bucket) -> flat buffer."""
+        parts = [torch.empty_like(shard) for _ in range(self.world)]
+        dist.all_gather(parts, shard, group=self.group)
+        full = torch.empty(self.n_padded, dtype=shard.dtype, device=shard.device)
+        for r, part in enumerate(parts):
+            full[shard_index_map(self.n_padded, self.world, r, self.bucket).to(shard.device)] = part
+        return full
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            torch.cuda.synchronize(self.device)
+            if dist.is_initialized():
+                dist.barrier(group=self.group)
+            _lib.load().nd_peer_ctx_destroy(self._h)
+            self._h = None
