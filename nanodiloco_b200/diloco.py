@@ -382,6 +382,50 @@ class Diloco:
         for p, v in zip(self._params, self.layout.views(full)):
             self.outer_optimizer.state[p]["momentum_buffer"] = v
 
+    # ---- state I/O (the reference has no checkpointing; this is what a checkpoint layer needs) -------
+    def _shard_indices(self):
+        """Global element indices of the elements this rank's master/momentum shard holds (None = all)."""
+        n = self.layout.total
+        if self._peer is not None:
+            lo, hi = self._peer.shard_range()
+            return torch.arange(lo, hi, device=self.device)
+        if self._nvls is not None or self._ctx is not None:
+            from .sync import shard_index_map
+            bucket = (self._nvls or self._ctx).bucket
+            return shard_index_map(n, self.world_size, self.rank, bucket).to(self.device)
+        return None
+
+    def _full(self, shard: torch.Tensor) -> torch.Tensor:
+        if shard.numel() == self.layout.total:
+            return shard.to(self.device)
+        return (self._peer or self._nvls or self._ctx).gather_shards(shard.to(self.device), *(
+            (self.layout.total,) if self._ctx is not None else ()))
+
+    def state_dict(self) -> dict:
+        """Everything the outer optimizer needs to resume, as full flat CPU tensors in `layout` order.
+        A COLLECTIVE when the state is sharded (every rank must call it; every rank gets the full state)."""
+        torch.cuda.current_stream(self.device).synchronize()
+        return {
+            "master": self._full(self._master).cpu(), "momentum": self._full(self._mom).cpu(),
+            "first_outer": self._first_outer, "inner_step_count": self._inner_step_count,
+            "numels": list(self.layout.numels), "offsets": list(self.layout.offsets), "total": self.layout.total,
+            "scheduler": self.scheduler.state_dict(),
+        }
+
+    def load_state_dict(self, sd: dict) -> None:
+        if list(sd["numels"]) != list(self.layout.numels) or sd["total"] != self.layout.total:
+            raise ValueError("state was saved for a different parameter layout or world size")
+        idx = self._shard_indices()
+        for name, dst in (("master", self._master), ("momentum", self._mom)):
+            src = sd[name].to(torch.float32)
+            if dst.numel() != self.layout.total:
+                src = src[idx.cpu()]
+            dst.copy_(src)
+        self._first_outer = bool(sd["first_outer"])
+        self._inner_step_count = int(sd["inner_step_count"])
+        self.scheduler.load_state_dict(sd["scheduler"])
+        self._publish_outer_state()
+
     # ------------------------------------------------------------------------------------------
     def inner_step(self):
         """diloco.py:56-60: clip_grad_norm_(1.0) -> AdamW step -> scheduler step -> zero_grad."""

@@ -161,3 +161,29 @@ def test_bf16_working_copy_wrapper():
         want16 = torch.from_numpy(master).to(torch.bfloat16).float().numpy()
         assert np.array_equal(flat32(params), want16)                  # working copy = bf16(master)
         assert np.array_equal(flat32([outer.state[p]["momentum_buffer"] for p in params]), mom)
+
+
+def test_state_dict_round_trip(golden_dir):
+    """Save after round 1, resume in a fresh wrapper, run round 2: same bits as the uninterrupted run."""
+    z = np.load(os.path.join(golden_dir, "outer_w1.npz"))
+
+    def drift(params, r):
+        loc, off = z[f"local_r{r}_w0"], 0
+        with torch.no_grad():
+            for p in params:
+                p.copy_(torch.from_numpy(loc[off:off + p.numel()]).reshape(p.shape))
+                off += p.numel()
+
+    model, inner, outer, d = _make(z, warmup_steps=2, total_steps=100)
+    drift(list(model.parameters()), 0)
+    d.outer_step()
+    sd = d.state_dict()
+    assert sd["master"].device.type == "cpu" and not sd["first_outer"]
+    model2, inner2, outer2, d2 = _make(z, warmup_steps=2, total_steps=100)
+    d2.load_state_dict(sd)
+    for r in (1, 2):
+        drift(list(model2.parameters()), r)
+        d2.outer_step()
+        assert np.array_equal(host(_flat(model2.parameters())), z[f"params_r{r}"])
+        mom = _flat([outer2.state[p]["momentum_buffer"] for p in model2.parameters()])
+        assert np.array_equal(host(mom), z[f"mom_r{r}"])

@@ -133,6 +133,11 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
                          first_step=(r == 0))
             ok &= np.array_equal(got, om) and np.array_equal(mom, ob)
     ok &= d.avg_sync_time > 0
+    sd = d.state_dict()                       # collective: full master and momentum on every rank
+    saved = torch.cat([v.reshape(-1) for v in d.layout.views(sd["master"])]).numpy()
+    ok &= np.array_equal(saved, _flat(params).cpu().numpy())        # just synced: theta_sync == params
+    d.load_state_dict(sd)                     # scatter back into this rank's shard: nothing changes
+    ok &= np.array_equal(d.state_dict()["momentum"].numpy(), sd["momentum"].numpy())
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:
