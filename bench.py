@@ -266,6 +266,32 @@ def _extras_n1(torch, _lib, dev, n, g, local, shapes, peak):
     return extras
 
 
+def _reference_gpu_outer_ms(torch, dist, dev, shapes, world):
+    """Wall ms of the reference's outer step (oracle/torch_reference.py port) with CUDA parameters and the
+    NCCL process group, max over ranks, best of 2."""
+    from oracle.torch_reference import ReferenceDilocoPort
+    g = torch.Generator(device=dev).manual_seed(1)
+    ps = [torch.nn.Parameter(torch.empty(sh, device=dev).normal_(0, 0.02, generator=g)) for sh in shapes]
+    inner_o = torch.optim.AdamW(ps, lr=4e-4)
+    outer_o = torch.optim.SGD(ps, lr=OUTER_LR, momentum=OUTER_MU, nesterov=True)
+    port = ReferenceDilocoPort(ps, inner_o, outer_o, 100, 10_000)
+    port.outer_step()
+    best = None
+    for _ in range(2):
+        dist.barrier()
+        torch.cuda.synchronize()
+        t_a = time.perf_counter()
+        port.outer_step()
+        torch.cuda.synchronize()
+        t = torch.tensor([(time.perf_counter() - t_a) * 1e3], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        best = float(t) if best is None else min(best, float(t))
+    del port, inner_o, outer_o, ps
+    torch.cuda.empty_cache()
+    return {"value": best, "what": f"the reference's outer_step (port) on {world} GPUs: per-tensor pageable H2D, sub, "
+            "NCCL all_reduce(AVG) per tensor, foreach SGD, clone + D2H; wall ms, max over ranks, best of 2"}
+
+
 def _tokens_per_s(torch, dist, dev, world, args):
     """tokens/s of the drop-in training loop (BASELINE configs[1] model size) on synthetic tokens."""
     tokens = None
@@ -546,6 +572,14 @@ def native_arm(args):
         except Exception as e:  # noqa: BLE001  (a failed side measurement must not lose the bench line)
             extras = {"error": repr(e)}
             torch.cuda.empty_cache()
+    # ---- N>1: the reference's own multi-GPU outer step on this box (per-tensor NCCL all_reduce(AVG) +
+    #      host-offloaded snapshot, diloco.py:46-54), the path to beat
+    if world > 1 and not args.no_extras:
+        try:
+            extras = {"reference_gpu_outer_step_ms": _reference_gpu_outer_ms(torch, dist, dev, shapes, world)}
+        except Exception as e:  # noqa: BLE001
+            extras = {"error": repr(e)}
+
     # ---- tokens/s: the drop-in training loop on synthetic tokens (BASELINE configs[1] model) -----
     tokens = None
     if not args.no_tokens:

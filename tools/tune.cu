@@ -155,6 +155,24 @@ int main(int argc, char** argv) {
     report("cudaMemcpyAsync D2D (8 B/elem)", time_ms([&] { CK(cudaMemcpyAsync(b, a, n * 4, cudaMemcpyDeviceToDevice)); }), 8.0 * n);
     report("copy_kernel float4 x2 (8 B/elem)", time_ms([&] { copy_kernel<<<sms * 4, 512>>>((float4*)a, (float4*)b, n / 4); }), 8.0 * n);
 
+    const bool tma_only = argc > 2;
+    if (tma_only) {
+        tma_fused<4096, 2, 512, 2>(a, b, c, n, sms);
+        tma_fused<4096, 2, 256, 2>(a, b, c, n, sms);
+        tma_fused<4096, 2, 1024, 2>(a, b, c, n, sms);
+        tma_fused<2048, 3, 256, 3>(a, b, c, n, sms);
+        tma_fused<8192, 2, 1024, 1>(a, b, c, n, sms);
+        tma_adam<2048, 2, 512, 2>(a, d, b, c, n, sms);
+        tma_adam<2048, 2, 512, 3>(a, d, b, c, n, sms);
+        tma_adam<2048, 2, 1024, 2>(a, d, b, c, n, sms);
+        tma_adam<1024, 2, 512, 4>(a, d, b, c, n, sms);
+        tma_adam<1024, 3, 512, 3>(a, d, b, c, n, sms);
+        tma_adam<1024, 2, 256, 5>(a, d, b, c, n, sms);
+        tma_adam<4096, 2, 1024, 1>(a, d, b, c, n, sms);
+        tma_adam<512, 3, 256, 6>(a, d, b, c, n, sms);
+        tma_adam<3072, 2, 768, 2>(a, d, b, c, n, sms);
+        return 0;
+    }
     fused_variant<1, 4>(a, b, c, n, sms);
     fused_variant<2, 4>(a, b, c, n, sms);
     fused_variant<1, 3>(a, b, c, n, sms);
