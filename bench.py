@@ -341,12 +341,15 @@ def reference_arm(args):
 
 
 def workload_config(args, n_total, n_tensors, world):
+    rep = max(1, getattr(args, "replicas", 1))
+    workers = world // rep
+    copy = "bf16 working copy, fp32 master and momentum" if getattr(args, "dtype", "f32") == "bf16" else "fp32"
     return {
-        "workload": (f"{args.workload} outer sync: {n_tensors} tensors, {n_total} fp32 params per worker, "
+        "workload": (f"{args.workload} outer sync: {n_tensors} tensors, {n_total} params per worker ({copy}), "
                      f"outer SGD lr {OUTER_LR} momentum {OUTER_MU} nesterov, steady-state (momentum warmed), "
-                     f"{world} worker(s), 1 per GPU"),
-        "l2": "each step streams >= 15 GB per GPU (>> 126 MB L2): inputs larger than L2, no flush needed",
-        "parallelism": f"diloco-dp{world}",
+                     f"{workers} worker(s), {rep} GPU(s) per worker"),
+        "l2": "each step streams several GB per GPU (>> 126 MB L2): inputs larger than L2, no flush needed",
+        "parallelism": f"diloco-dp{workers}" + (f"x{rep}" if rep > 1 else ""),
     }
 
 
@@ -373,13 +376,19 @@ def native_arm(args):
 
     shapes = workload_shapes(args.workload)
     metas = [torch.empty(s, device="meta") for s in shapes]
-    layout = FlatLayout.plan(metas, quantum=4 * world)
+    bf16 = args.dtype == "bf16"
+    wdtype = torch.bfloat16 if bf16 else torch.float32
+    gran = 8 if bf16 else 4
+    layout = FlatLayout.plan(metas, quantum=gran * world, align=gran)
     n_real = sum(numel(s) for s in shapes)
     n = layout.total
     K, Wm = args.steps, max(3, args.warmup)
 
     from nanodiloco_b200.sync import PeerContext
     mode = "none" if world == 1 else args.sync
+    if (bf16 or args.replicas > 1) and mode not in ("none", "p2p"):
+        raise SystemExit("--dtype bf16 / --replicas need the peer-memory sync (--sync p2p)")
+    workers = world // max(1, args.replicas)
     g = torch.Generator(device=dev).manual_seed(0)
     master = torch.empty(n, device=dev).normal_(0, 0.02, generator=g)      # same on every rank (seed 0)
     gl = torch.Generator(device=dev).manual_seed(100 + rank)
@@ -387,10 +396,12 @@ def native_arm(args):
     ctx = pctx = None
     if mode == "p2p":
         # one fused kernel per GPU over NVLink peer memory; master and momentum sharded 1/W
-        pctx = PeerContext(world, rank, n, group=None, device=dev)
-        local = pctx.local()[:n]
-        local.copy_(master)
-        local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))
+        pctx = PeerContext(world, rank, n, elem_bytes=2 if bf16 else 4, group=None, device=dev,
+                           replicas=args.replicas)
+        local = pctx.local(wdtype)[:n]
+        # replicas of one worker hold identical parameters: seed the drift per worker, not per rank
+        gl = torch.Generator(device=dev).manual_seed(100 + rank // max(1, args.replicas))
+        local.copy_(master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))
         lo, hi = pctx.shard_range()
         master = master[lo:hi].clone()
         mom = torch.zeros(hi - lo, device=dev)
@@ -398,7 +409,7 @@ def native_arm(args):
         torch.cuda.empty_cache()
 
         def step(first=False):
-            pctx.outer_sync(master, mom, first_step=first, **hyper)
+            pctx.outer_sync(master, mom, dtype=wdtype, first_step=first, **hyper)
     elif mode == "nvls":
         # in-switch reduction (multimem) over torch symmetric memory; full master replica
         from nanodiloco_b200.sync import NvlsContext
@@ -413,14 +424,17 @@ def native_arm(args):
         def step(first=False):
             nctx.outer_sync(master, mom, first_step=first, **hyper)
     else:
-        local = master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)
+        local = (master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)).to(wdtype)
         ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
                           device=dev)
         mom = torch.zeros(ctx.shard_elems(n), device=dev)
         pg = torch.empty(n, device=dev) if world > 1 else None
 
         def step(first=False):
-            ctx.outer_sync(local, master, mom, pg, first_step=first, **hyper)
+            if world == 1:
+                _lib.outer_fused(master, mom, [local], first_step=first, **hyper)
+            else:
+                ctx.outer_sync(local, master, mom, pg, first_step=first, **hyper)
 
     def barrier():
         if world > 1:
@@ -428,7 +442,7 @@ def native_arm(args):
         torch.cuda.synchronize()
 
     step(first=True)                                    # first-step branch, also warms the momentum
-    local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))   # drift again
+    local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl).to(wdtype))   # drift again
     for _ in range(Wm):
         step()
     sampler = ClockSampler(local_rank) if rank == 0 else None
@@ -453,8 +467,9 @@ def native_arm(args):
     # ---- the dominant kernel alone, CUDA events on its launching stream -------------------------
     # N=1: the step IS one launch of the fused kernel (24 B/elem).  N>1: kernel (1) pseudo-gradient
     # over the whole space (12 B/elem) is the largest HBM mover; time it on its own.
+    lb = 2.0 if bf16 else 4.0                                  # bytes per element of the working copy
     if world == 1:
-        kern_ms, kern_bytes, kern_name = ms, 24.0 * n, "outer_fused<W=1> (tma::tile_kernel)"
+        kern_ms, kern_bytes, kern_name = ms, (16.0 + 2 * lb) * n, "outer_fused<W=1> (tma::tile_kernel)"
     elif mode == "nvls":
         kern_ms, kern_bytes = ms, (12.0 + 8.0 + 8.0 * (world - 1) / world + 16.0 / world) * n
         kern_name = f"K1 + nvls_shard_kernel (multimem.ld_reduce / multimem.st) + master refresh, W={world}"
@@ -462,8 +477,8 @@ def native_arm(args):
         # the step IS one launch of the fused kernel over this rank's shard (+ two flag barriers);
         # HBM bytes this GPU moves for it: its copy is read once and written once by the W owners
         # (8 B/elem) and it reads+writes its master and momentum shards (16/W B/elem)
-        kern_ms, kern_bytes = ms, (8.0 + 16.0 / world) * n
-        kern_name = f"outer_fused<W={world}> over peer memory (tma::tile_kernel), NVLink-bound"
+        kern_ms, kern_bytes = ms, (2 * lb + 16.0 / world) * n
+        kern_name = f"outer_fused<W={workers}> over peer memory (tma::tile_kernel), NVLink-bound"
     else:
         k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
@@ -493,8 +508,9 @@ def native_arm(args):
                 "algorithmic_bytes_per_launch": kern_bytes, "kernel_ms": kern_ms}
 
     # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
-    hbm_bytes = (24.0 if world == 1 else (8.0 + 16.0 / world if mode == "p2p" else 12.0 + 24.0 / world)) * n
-    nvl_bytes = 0.0 if world == 1 else 8.0 * (world - 1) / world * n   # reduce-scatter + all-gather bytes (the roofline)
+    hbm_bytes = ((16.0 + 2 * lb) if world == 1 else (2 * lb + 16.0 / world if mode == "p2p" else 12.0 + 24.0 / world)) * n
+    # reduce-scatter + all-gather bytes of the working copy, per direction per GPU (the roofline)
+    nvl_bytes = 0.0 if world == 1 else 2 * lb * (world - 1) / world * n
     step_roof = {"hbm_algorithmic_gbs": hbm_bytes / (ms * 1e-3) / 1e9,
                  "nvlink_algorithmic_gbs_per_dir": nvl_bytes / (ms * 1e-3) / 1e9,
                  "t_hbm_ms": hbm_bytes / (peak * 1e9) * 1e3, "t_nvlink_ms_at_900": nvl_bytes / 900e9 * 1e3}
@@ -612,7 +628,7 @@ def native_arm(args):
         line = {
             "metric": METRIC, "value": ms, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
             "ms_per_step": ms, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
+            "dtype": "f32" if not bf16 else "f32 master/momentum, bf16 working copy", "data": "synthetic",
             "config": workload_config(args, n_real, len(shapes), world),
             "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "clocks": sampler.summary() if sampler else None,
@@ -640,6 +656,10 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="llama1b")
     ap.add_argument("--bucket-mb", type=float, default=64.0)
     ap.add_argument("--streams", type=int, default=2)
+    ap.add_argument("--dtype", choices=["f32", "bf16"], default="f32",
+                    help="working-copy dtype; bf16 = 'bf16 inner / fp32 outer' of BASELINE configs[1] (extension)")
+    ap.add_argument("--replicas", type=int, default=1,
+                    help="GPUs per DiLoCo worker (BASELINE configs[4]: 4 workers x 2 GPUs = --gpus 8 --replicas 2)")
     ap.add_argument("--sync", choices=["p2p", "nccl", "nvls"], default="p2p",
                     help="N>1: fused peer-memory kernel (default) or bucketed NCCL reduce-scatter/all-gather")
     ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
