@@ -84,7 +84,9 @@ def library_path() -> str:
 
 
 def load() -> ctypes.CDLL:
-    """Loads the CUDA library, building it first when the source is newer and nvcc exists.
+    """Loads the CUDA library, building it first (under a lock, atomically) only when it is missing
+    and nvcc exists.  An existing library is trusted; `python -m nanodiloco_b200.build --force` or
+    `__graft_entry__.build()` rebuild it.
 
     Fails loudly otherwise -- there is no CPU or PyTorch fallback for this path."""
     global _lib

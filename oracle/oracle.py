@@ -22,10 +22,19 @@ _lib = None
 
 
 def build(force: bool = False) -> str:
-    """Compile nd_oracle.c with gcc (seconds).  Building the checker is not using it."""
-    src = os.path.join(_HERE, "nd_oracle.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
-        subprocess.check_call(["make", "-s", "-C", _HERE, "libnd_oracle.so"])
+    """Compile nd_oracle.c with gcc (seconds) when the library is missing (or `force`).  Built into a
+    temporary file and renamed into place under a lock.  Building the checker is not using it."""
+    import fcntl
+    if not force and os.path.exists(_SO):
+        return _SO
+    with open(_SO + ".lock", "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        if force or not os.path.exists(_SO):
+            tmp = f"{_SO}.tmp.{os.getpid()}"
+            subprocess.check_call(["gcc", "-O2", "-fPIC", "-shared", "-ffp-contract=off", "-fopenmp", "-Wall", "-Wextra",
+                                   "-o", tmp, os.path.join(_HERE, "nd_oracle.c"), "-lm"])
+            os.replace(tmp, _SO)
+        fcntl.flock(lock, fcntl.LOCK_UN)
     return _SO
 
 
