@@ -224,17 +224,18 @@ class Diloco:
             self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
             self._grad_views = self.layout.views(self._grad)
             self._attach_grads()
-            # same keys torch.optim.AdamW creates lazily (torch:optim/adam.py:167-190)
+            # same keys torch.optim.AdamW creates lazily (torch:optim/adam.py:167-190).  Every parameter
+            # takes the same step every time, so all of them share ONE host step counter: a single
+            # increment per inner step instead of one per tensor.
+            self._step_tensor = torch.tensor(0.0, dtype=torch.float32)
             for p, m, v in zip(self._params, self.layout.views(self._exp_avg), self.layout.views(self._exp_avg_sq)):
                 st = self.inner_optimizer.state[p]
-                if len(st) == 0:
-                    st["step"] = torch.tensor(0.0, dtype=torch.float32)
-                    st["exp_avg"] = m
-                    st["exp_avg_sq"] = v
-                else:  # caller resumed an optimizer: adopt its moments
+                if len(st) != 0:  # caller resumed an optimizer: adopt its moments and step count
                     m.copy_(st["exp_avg"]); v.copy_(st["exp_avg_sq"])
-                    st["exp_avg"], st["exp_avg_sq"] = m, v
                     self._inner_step_count = int(st["step"])
+                st["exp_avg"], st["exp_avg_sq"] = m, v
+                st["step"] = self._step_tensor
+            self._step_tensor.fill_(float(self._inner_step_count))
             self._inner_ranges = self._group_ranges(self.inner_optimizer)
         self._outer_ranges = self._group_ranges(self.outer_optimizer)
 
@@ -456,8 +457,7 @@ class Diloco:
                        lr=float(g["lr"]), beta1=float(b1), beta2=float(b2), eps=float(g["eps"]),
                        weight_decay=float(g["weight_decay"]), step=self._inner_step_count,
                        sumsq_dev=self._sumsq, max_norm=self.max_grad_norm, zero_grad=True)
-        for p in self._params:
-            self.inner_optimizer.state[p]["step"] += 1
+        self._step_tensor += 1
         # the fused kernel stood in for inner_optimizer.step(); tell the LR scheduler's order check so
         self.inner_optimizer._opt_called = True
         self.scheduler.step()
