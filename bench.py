@@ -37,9 +37,8 @@ WORKLOADS = {"llama1b": "llama1b", "llama150m": "llama150m", "tiny": "tiny"}
 
 
 def workload_shapes(name: str):
-    # shape tables only (no arithmetic): shared with the tests
-    from oracle.torch_reference import CONFIGS, llama_shapes
-    return llama_shapes(**CONFIGS[name])
+    from nanodiloco_b200.workloads import workload_shapes as _ws   # shape tables only
+    return _ws(name)
 
 
 def numel(shape) -> int:

@@ -353,6 +353,8 @@ class Diloco:
                                  nesterov=bool(g["nesterov"]), first_step=first)
         t1.record(stream)
         self._pending_events.append((t0, t1))
+        if len(self._pending_events) > 32:      # fold finished timings in; old events completed long ago
+            self.avg_sync_time
         self._first_outer = False
         self._publish_outer_state()
         # diloco.py:53 -- outer_optimizer.zero_grad(): the pseudo-gradient never became .grad here

@@ -111,3 +111,16 @@ def test_llama_shape_tables():
         shapes = llama_shapes(**CONFIGS[name])
         assert len(shapes) == tensors
         assert sum(int(np.prod(s)) for s in shapes) == elems
+        from nanodiloco_b200.workloads import workload_shapes       # the product's own copy of the table
+        assert workload_shapes(name) == shapes
+
+
+def test_shape_table_matches_the_real_model():
+    transformers = pytest.importorskip("transformers")
+    cfg = transformers.LlamaConfig(hidden_size=128, intermediate_size=512, num_attention_heads=4,
+                                   num_hidden_layers=6, rms_norm_eps=1e-5, use_cache=False)   # configs/llama_default.json
+    with torch.device("meta"):
+        model = transformers.LlamaForCausalLM(cfg)
+    got = [tuple(p.shape) for p in model.parameters()]
+    assert sorted(got) == sorted(llama_shapes(**CONFIGS["tiny"]))
+    assert sum(int(np.prod(s)) for s in got) == 9_766_528
