@@ -236,7 +236,7 @@ class Diloco:
                 st["exp_avg"], st["exp_avg_sq"] = m, v
                 st["step"] = self._step_tensor
             self._step_tensor.fill_(float(self._inner_step_count))
-            self._inner_ranges = self._group_ranges(self.inner_optimizer)
+            self._inner_ranges = self._trainable_runs(self.inner_optimizer)
         self._outer_ranges = self._group_ranges(self.outer_optimizer)
 
         # diloco.py:23-24 declares these and never updates them; here they are real
@@ -259,9 +259,31 @@ class Diloco:
             out[-1] = (g, s, self.layout.total)
         return out
 
+    def _trainable_runs(self, optimizer):
+        """(group, start, end) ranges covering maximal runs of consecutive TRAINABLE tensors of each
+        param group.  torch's AdamW never touches a parameter whose `.grad` is None -- which is what a
+        frozen (`requires_grad=False`) parameter has -- so frozen tensors must not even see weight decay;
+        they still take part in the outer sync (their pseudo-gradient is zero)."""
+        out, i = [], 0
+        for g in optimizer.param_groups:
+            run_start = None
+            for j, p in enumerate(g["params"]):
+                k = i + j
+                if p.requires_grad:
+                    if run_start is None:
+                        run_start = k
+                    last = k
+                if (not p.requires_grad or j == len(g["params"]) - 1) and run_start is not None:
+                    s, e = self.layout.span(run_start, last)
+                    out.append((g, s, e))
+                    run_start = None
+            i += len(g["params"])
+        return out
+
     def _attach_grads(self) -> None:
         for p, gv in zip(self._params, self._grad_views):
-            p.grad = gv
+            if p.requires_grad:
+                p.grad = gv
 
     def _pick_sync_mode(self, dev) -> str:
         """'p2p' when every rank sits on this node and can map every other rank's memory."""
@@ -443,7 +465,7 @@ class Diloco:
             self.inner_optimizer.zero_grad()
             return
         flat_ok = all(p.grad is not None and p.grad.data_ptr() == gv.data_ptr()
-                      for p, gv in zip(self._params, self._grad_views))
+                      for p, gv in zip(self._params, self._grad_views) if p.requires_grad)
         if not flat_ok:
             self._adopt_foreign_grads()
         self._inner_step_count += 1
@@ -471,6 +493,8 @@ class Diloco:
         fold those gradients into the flat buffer and re-attach the views."""
         with torch.no_grad():
             for p, gv in zip(self._params, self._grad_views):
+                if not p.requires_grad:
+                    continue
                 if p.grad is None:
                     gv.zero_()
                 elif p.grad.data_ptr() != gv.data_ptr():

@@ -187,3 +187,24 @@ def test_state_dict_round_trip(golden_dir):
         assert np.array_equal(host(_flat(model2.parameters())), z[f"params_r{r}"])
         mom = _flat([outer2.state[p]["momentum_buffer"] for p in model2.parameters()])
         assert np.array_equal(host(mom), z[f"mom_r{r}"])
+
+
+def test_frozen_parameters_are_left_alone_by_the_inner_step():
+    """torch's AdamW skips parameters without a gradient: a frozen tensor must not even be weight-decayed."""
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(16, 16), torch.nn.Linear(16, 16), torch.nn.Linear(16, 4)).cuda()
+    for p in model[1].parameters():
+        p.requires_grad_(False)
+    ref = [p.detach().clone() for p in model.parameters()]
+    inner = torch.optim.AdamW(model.parameters(), lr=1e-2, weight_decay=0.1)
+    outer = torch.optim.SGD(model.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(model, inner, outer, warmup_steps=0, total_steps=20)
+    x = torch.randn(8, 16, device="cuda")
+    for _ in range(3):
+        d(x).square().mean().backward()
+        d.inner_step()
+    ps = list(model.parameters())
+    assert torch.equal(ps[2], ref[2]) and torch.equal(ps[3], ref[3])          # frozen: bit-identical
+    assert not torch.equal(ps[0], ref[0]) and not torch.equal(ps[4], ref[4])  # trainable: moved
+    d.outer_step()
+    assert torch.equal(ps[2], ref[2])                                         # zero pseudo-gradient

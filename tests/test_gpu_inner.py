@@ -145,3 +145,26 @@ def test_adamw_bf16_working_copy_vs_oracle(n):
         assert np.array_equal(host(m), m_np) and np.array_equal(host(v), v_np), step
         assert torch.equal(p16.cpu(), torch.from_numpy(p_np).to(torch.bfloat16)), step
         assert float(g16.float().abs().max()) == 0.0
+
+
+def test_adamw_nonfinite_gradients_match_torch():
+    """An inf in the gradients: torch's clip makes the coefficient 0, inf*0 = NaN poisons exactly that
+    element's moments and parameter, everything else sees a zero gradient.  Same here."""
+    n = 10_000
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    ref = torch.nn.Parameter(torch.randn(n, device="cuda", generator=gen) * 0.02)
+    opt = torch.optim.AdamW([ref], lr=1e-3)
+    p, m, v = ref.data.clone(), torch.zeros(n, device="cuda"), torch.zeros(n, device="cuda")
+    g = torch.randn(n, device="cuda", generator=gen) * 0.01
+    g[123] = float("inf")
+    ref.grad = g.clone()
+    torch.nn.utils.clip_grad_norm_([ref], 1.0)
+    opt.step()
+    ss, sc = torch.zeros(1, device="cuda"), _lib.scratch("cuda")
+    _lib.sumsq(g, ss, sc)
+    _lib.adamw(p, g.clone(), m, v, lr=1e-3, step=1, sumsq_dev=ss, max_norm=1.0)
+    assert torch.isinf(ss).all()
+    assert torch.equal(torch.isnan(p), torch.isnan(ref.data)) and int(torch.isnan(p).sum()) == 1
+    ok = ~torch.isnan(p)
+    torch.testing.assert_close(p[ok], ref.data[ok], rtol=2e-6, atol=1e-9)
+    assert torch.equal(torch.isnan(m), torch.isnan(opt.state[ref]["exp_avg"]))
