@@ -498,7 +498,7 @@ def native_arm(args):
     if os.path.exists(tpath):
         try:
             tj = json.load(open(tpath))
-            if world == 1 and tj.get("kernel") == "outer_fused_w1" and tj.get("elems"):
+            if world == 1 and not bf16 and tj.get("kernel") == "outer_fused_w1" and tj.get("elems"):
                 traffic = tj["dram_bytes_per_launch"] * (n / tj["elems"])
         except Exception:  # noqa: BLE001
             traffic = None
