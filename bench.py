@@ -409,10 +409,11 @@ def native_arm(args):
 
         def step(first=False):
             pctx.outer_sync(master, mom, dtype=wdtype, first_step=first, **hyper)
-    elif mode == "nvls":
+    elif mode in ("nvls", "hybrid"):
         # in-switch reduction (multimem) over torch symmetric memory; full master replica
         from nanodiloco_b200.sync import NvlsContext
-        nctx = NvlsContext(world, rank, n, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, device=dev)
+        nctx = NvlsContext(world, rank, n, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, device=dev,
+                           nvls_fraction=1.0 if mode == "nvls" else args.nvls_fraction)
         local = nctx.local()
         local.copy_(master)
         local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl))
@@ -469,7 +470,7 @@ def native_arm(args):
     lb = 2.0 if bf16 else 4.0                                  # bytes per element of the working copy
     if world == 1:
         kern_ms, kern_bytes, kern_name = ms, (16.0 + 2 * lb) * n, "outer_fused<W=1> (tma::tile_kernel)"
-    elif mode == "nvls":
+    elif mode in ("nvls", "hybrid"):
         kern_ms, kern_bytes = ms, (12.0 + 8.0 + 8.0 * (world - 1) / world + 16.0 / world) * n
         kern_name = f"K1 + nvls_shard_kernel (multimem.ld_reduce / multimem.st) + master refresh, W={world}"
     elif mode == "p2p":
@@ -615,7 +616,7 @@ def native_arm(args):
         except Exception as e:  # noqa: BLE001
             cpu_baseline = {"error": repr(e)}
 
-    if mode == "nvls":
+    if mode in ("nvls", "hybrid"):
         launches_per_step = 4                                          # K1, barrier, NVLS kernel, barrier
     elif mode == "p2p":
         launches_per_step = 3                                          # barrier, fused kernel, barrier
@@ -633,7 +634,8 @@ def native_arm(args):
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
             "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
-            "bucket_mb": args.bucket_mb if mode in ("nccl", "nvls") else None, "sync": mode, "extras": extras, "tokens_per_s": tokens,
+            "nvls_fraction": args.nvls_fraction if mode == "hybrid" else None,
+            "bucket_mb": args.bucket_mb if mode in ("nccl", "nvls", "hybrid") else None, "sync": mode, "extras": extras, "tokens_per_s": tokens,
         }
         print(json.dumps(line), flush=True)
     if ctx is not None:
@@ -659,7 +661,8 @@ def main():
                     help="working-copy dtype; bf16 = 'bf16 inner / fp32 outer' of BASELINE configs[1] (extension)")
     ap.add_argument("--replicas", type=int, default=1,
                     help="GPUs per DiLoCo worker (BASELINE configs[4]: 4 workers x 2 GPUs = --gpus 8 --replicas 2)")
-    ap.add_argument("--sync", choices=["p2p", "nccl", "nvls"], default="p2p",
+    ap.add_argument("--nvls-fraction", type=float, default=0.75, help="--sync hybrid: share of the space reduced in-switch")
+    ap.add_argument("--sync", choices=["p2p", "nccl", "nvls", "hybrid"], default="p2p",
                     help="N>1: fused peer-memory kernel (default) or bucketed NCCL reduce-scatter/all-gather")
     ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
     ap.add_argument("--e2e-steps", type=int, default=5)

@@ -343,6 +343,17 @@ int nd_outer_sync_nvls(nd_peer_ctx* ctx, float* local, float* pg, float* mc_loca
                        float* master, float* mom_shard, int64_t n_padded, int64_t bucket_elems,
                        float lr, float mu, float dampening, float wd, int nesterov, int first_step,
                        nd_stream_t stream);
+/* nd_outer_sync_nvls on the first n_nvls elements and, concurrently on a fourth internal stream,
+ * the peer-memory fused kernel (nd_outer_fused_rw over the mapped copies) on the rest
+ * [n_nvls, n_padded), cut into `world` contiguous shards.  The in-switch reduction sustains fewer
+ * link bytes per second than plain peer traffic; splitting the space lets the two mechanisms share
+ * the links.  n_nvls: multiple of 4*world in [0, n_padded] (n_padded = pure NVLS, 0 = pure peer
+ * kernel with a full master replica).  mom_shard: the in-switch part's n_nvls/world elements (bucket
+ * order) followed by the peer part's (n_padded - n_nvls)/world. */
+int nd_outer_sync_hybrid(nd_peer_ctx* ctx, float* local, float* pg, float* mc_local, float* mc_pg,
+                         float* master, float* mom_shard, int64_t n_padded, int64_t n_nvls,
+                         int64_t bucket_elems, float lr, float mu, float dampening, float wd,
+                         int nesterov, int first_step, nd_stream_t stream);
 int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
 
 #ifdef __cplusplus

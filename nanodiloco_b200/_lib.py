@@ -69,6 +69,8 @@ SIGNATURES = {
     "nd_peer_ctx_create_from_ptrs": (_c_i, [_c_i, _c_i, ctypes.POINTER(_c_p), ctypes.c_size_t, ctypes.POINTER(_c_p)]),
     "nd_outer_sync_nvls": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_i64, _c_i64, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i,
                                   _c_p]),
+    "nd_outer_sync_hybrid": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_i64, _c_i64, _c_i64, _c_f, _c_f, _c_f,
+                                    _c_f, _c_i, _c_i, _c_p]),
     "nd_peer_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
 }
 

@@ -113,9 +113,9 @@ struct nd_peer_ctx {
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timed = false;
     // side streams for the host-resident-master variant (created on first use)
-    static constexpr int kStreams = 3;
-    cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr};
-    cudaEvent_t done[kStreams] = {nullptr, nullptr, nullptr};
+    static constexpr int kStreams = 4;
+    cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t done[kStreams] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t fork = nullptr;
     std::vector<cudaEvent_t> bucket_events;  // NVLS pipeline: two per bucket
 };
@@ -320,7 +320,7 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float*
     int64_t k = 0;
     for (int64_t off = 0; off < shard; off += chunk_elems, ++k) {
         const int64_t len = (shard - off < chunk_elems) ? (shard - off) : chunk_elems;
-        const int slot = (int)(k % nd_peer_ctx::kStreams);
+        const int slot = (int)(k % 3);  // three staging slots (see the header), one stream each
         cudaStream_t s = c->streams[slot];  // stream order also keeps a slot from being reused too early
         float* m_dev = staging + (int64_t)slot * chunk_elems;
         ND_CUDA(cudaMemcpyAsync(m_dev, master_host_shard + off, (size_t)len * 4, cudaMemcpyHostToDevice, s));
@@ -372,9 +372,9 @@ static int nvls_launch(nd_peer_ctx* c, float* master, float* mom, const float* m
     return check_launch("nvls_shard_kernel");
 }
 
-int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local, float* mc_pg, float* master,
-                       float* mom_shard, int64_t n_padded, int64_t bucket_elems, float lr, float mu, float dampening,
-                       float wd, int nesterov, int first_step, nd_stream_t stream_) {
+int nd_outer_sync_hybrid(nd_peer_ctx* c, float* local, float* pg, float* mc_local, float* mc_pg, float* master,
+                         float* mom_shard, int64_t n_padded, int64_t n_nvls, int64_t bucket_elems, float lr, float mu,
+                         float dampening, float wd, int nesterov, int first_step, nd_stream_t stream_) {
     if (!c) return set_error(ND_ESTATE, "nd_outer_sync_nvls: null context");
     const int W = c->world;
     if (c->replicas != 1) return set_error(ND_ESTATE, "nd_outer_sync_nvls: replicas are not supported");
@@ -385,9 +385,11 @@ int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local,
     if (n_padded && (!local || !pg || !mc_local || !mc_pg || !master || !mom_shard))
         return set_error(ND_EINVAL, "nd_outer_sync_nvls: null pointer");
     if (bucket_elems < 1) return set_error(ND_EINVAL, "nd_outer_sync_nvls: bucket_elems < 1");
+    if (n_nvls < 0 || n_nvls > n_padded || n_nvls % q != 0)
+        return set_error(ND_EINVAL, "nd_outer_sync_hybrid: n_nvls must be a multiple of 4*world in [0, n_padded]");
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const int64_t bucket = (bucket_elems + q - 1) / q * q;
-    const int64_t nb = (n_padded + bucket - 1) / bucket;
+    const int64_t nb = (n_nvls + bucket - 1) / bucket;
     const OuterHyper h{-lr, mu, 1.0f - dampening, wd, nesterov, first_step};
     int rc;
     if ((rc = ensure_side_streams(c))) return rc;
@@ -396,7 +398,7 @@ int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local,
     //   lane B  barrier(all ranks' pg_b are in memory) -> in-switch sum + update + multicast store   (NVLink)
     //   lane C  barrier(every copy of bucket b is written) -> master replica refresh of bucket b       (HBM)
     // so the HBM-only passes of buckets b+1 and b-1 hide under the NVLink pass of bucket b.
-    cudaStream_t sa = c->streams[0], sb = c->streams[1], sc = c->streams[2];
+    cudaStream_t sa = c->streams[0], sb = c->streams[1], sc = c->streams[2], sd = c->streams[3];
     ND_CUDA(cudaEventRecord(c->t0, stream));
     ND_CUDA(cudaEventRecord(c->fork, stream));
     for (int i = 0; i < nd_peer_ctx::kStreams; ++i) ND_CUDA(cudaStreamWaitEvent(c->streams[i], c->fork, 0));
@@ -406,9 +408,29 @@ int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local,
         for (size_t i = old; i < c->bucket_events.size(); ++i)
             ND_CUDA(cudaEventCreateWithFlags(&c->bucket_events[i], cudaEventDisableTiming));
     }
+    // Region B = [n_nvls, n_padded): the peer-memory fused kernel on its own lane, concurrently.  The
+    // in-switch path tops out below what the links carry (the switch's reduction rate), so handing
+    // part of the space to plain peer loads/stores uses the bandwidth it leaves idle.
+    if (n_padded > n_nvls) {
+        const int64_t sB = (n_padded - n_nvls) / W, mineB = n_nvls + (int64_t)c->rank * sB;
+        if ((rc = peer_barrier_ch(c, 3, sd))) return rc;  // every worker's inner steps are done
+        void *reads[ND_MAX_WORKERS], *writes[ND_MAX_WORKERS];
+        const int workers = fill_rw(c, (size_t)mineB * 4, reads, writes);
+        if ((rc = nd_outer_fused_rw(master + mineB, mom_shard + n_nvls / W, reads, workers, writes, W, ND_F32, sB, lr,
+                                    mu, dampening, wd, nesterov, first_step, nullptr, nullptr,
+                                    reinterpret_cast<nd_stream_t>(sd))))
+            return rc;
+        if ((rc = peer_barrier_ch(c, 3, sd))) return rc;  // every shard of region B has been written
+        if (mineB > n_nvls)
+            ND_CUDA(cudaMemcpyAsync(master + n_nvls, local + n_nvls, (size_t)(mineB - n_nvls) * 4,
+                                    cudaMemcpyDeviceToDevice, sd));
+        if (mineB + sB < n_padded)
+            ND_CUDA(cudaMemcpyAsync(master + mineB + sB, local + mineB + sB, (size_t)(n_padded - mineB - sB) * 4,
+                                    cudaMemcpyDeviceToDevice, sd));
+    }
     for (int64_t b = 0; b < nb; ++b) {
         const int64_t off = b * bucket;
-        const int64_t len = (n_padded - off < bucket) ? (n_padded - off) : bucket;
+        const int64_t len = (n_nvls - off < bucket) ? (n_nvls - off) : bucket;
         const int64_t slice = len / W, mine = off + (int64_t)c->rank * slice;
         const int64_t shard_off = b * (bucket / W);
         cudaEvent_t k1_done = c->bucket_events[2 * b], upd_done = c->bucket_events[2 * b + 1];
@@ -436,6 +458,13 @@ int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local,
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
     return ND_OK;
+}
+
+int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local, float* mc_pg, float* master,
+                       float* mom_shard, int64_t n_padded, int64_t bucket_elems, float lr, float mu, float dampening,
+                       float wd, int nesterov, int first_step, nd_stream_t stream_) {
+    return nd_outer_sync_hybrid(c, local, pg, mc_local, mc_pg, master, mom_shard, n_padded, n_padded, bucket_elems, lr,
+                                mu, dampening, wd, nesterov, first_step, stream_);
 }
 
 int nd_peer_last_ms(nd_peer_ctx* c, float* ms_out) {

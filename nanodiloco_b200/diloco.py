@@ -73,6 +73,7 @@ class Diloco:
         offload_chunk_mb: float = 64.0,
         sync: str = "auto",
         replicas_per_worker: int = 1,
+        nvls_fraction: float = 0.75,
     ):
         # diloco.py:17-20
         self.model = model
@@ -143,19 +144,21 @@ class Diloco:
         #   "nvls" in-switch reduction (multimem.ld_reduce / multimem.st over symmetric memory,
         #          nd_outer_sync_nvls): fewest NVLink bytes; full master replica; fp32; the sum order
         #          is the switch's, so W > 2 matches the reference within tolerance, not bit for bit.
-        if sync not in ("auto", "p2p", "nccl", "nvls"):
-            raise ValueError("sync must be 'auto', 'p2p', 'nccl' or 'nvls'")
+        #   "hybrid" nvls on `nvls_fraction` of the space and the peer kernel on the rest, concurrently.
+        if sync not in ("auto", "p2p", "nccl", "nvls", "hybrid"):
+            raise ValueError("sync must be 'auto', 'p2p', 'nccl', 'nvls' or 'hybrid'")
         self.sync_mode = "none" if W == 1 else (self._pick_sync_mode(dev) if sync == "auto" else sync)
         if self.replicas > 1 and self.sync_mode != "p2p":  # (nvls: checked below)
             raise NotImplementedError("replicas_per_worker > 1 needs the peer-memory sync (sync='p2p')")
         self._peer = None
         self._nvls = None
-        if self.sync_mode == "nvls":
+        if self.sync_mode in ("nvls", "hybrid"):
             if wdtype != torch.float32 or offload_master or self.replicas > 1:
                 raise NotImplementedError("sync='nvls' handles an fp32 working copy, resident master, one rank per worker")
             from .sync import NvlsContext
             self._nvls = NvlsContext(W, self.rank, n, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
-                                     group=process_group, device=dev)
+                                     group=process_group, device=dev,
+                                     nvls_fraction=1.0 if self.sync_mode == "nvls" else nvls_fraction)
             self._local = self._nvls.local()
         elif self.sync_mode == "p2p":
             from .sync import PeerContext
@@ -414,10 +417,11 @@ class Diloco:
         if self._peer is not None:
             lo, hi = self._peer.shard_range()
             return torch.arange(lo, hi, device=self.device)
-        if self._nvls is not None or self._ctx is not None:
+        if self._nvls is not None:
+            return self._nvls.shard_indices().to(self.device)
+        if self._ctx is not None:
             from .sync import shard_index_map
-            bucket = (self._nvls or self._ctx).bucket
-            return shard_index_map(n, self.world_size, self.rank, bucket).to(self.device)
+            return shard_index_map(n, self.world_size, self.rank, self._ctx.bucket).to(self.device)
         return None
 
     def _full(self, shard: torch.Tensor) -> torch.Tensor:

@@ -230,10 +230,16 @@ class NvlsContext:
     """
 
     def __init__(self, world: int, rank: int, n_padded: int, *, bucket_elems: int = 1 << 25, group=None,
-                 device=None):
+                 device=None, nvls_fraction: float = 1.0):
         import torch.distributed._symmetric_memory as symm
         q = 4 * world
         self.bucket = (int(bucket_elems) + q - 1) // q * q
+        # hybrid: the first n_nvls elements go through the switch, the rest through the peer kernel
+        if not 0.0 <= nvls_fraction <= 1.0:
+            raise ValueError("nvls_fraction must be in [0, 1]")
+        self.n_nvls = min(int(n_padded), int(int(n_padded) * nvls_fraction) // q * q)
+        if nvls_fraction >= 1.0:
+            self.n_nvls = int(n_padded)
         L = _lib.load()
         self.world, self.rank, self.group = world, rank, group
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
@@ -273,10 +279,10 @@ class NvlsContext:
     def outer_sync(self, master, mom_shard, *, lr, momentum, dampening=0.0, weight_decay=0.0, nesterov=True,
                    first_step=False, stream=None) -> None:
         _lib._require_cuda(master, mom_shard)
-        _lib.check(_lib.load().nd_outer_sync_nvls(
+        _lib.check(_lib.load().nd_outer_sync_hybrid(
             self._h, self.local().data_ptr(), self.pg().data_ptr(), self.mc_local, self.mc_pg, _lib._ptr(master),
-            _lib._ptr(mom_shard), self.n_padded, self.bucket, lr, momentum, dampening, weight_decay, int(nesterov),
-            int(first_step), _lib._stream(stream)), "nd_outer_sync_nvls")
+            _lib._ptr(mom_shard), self.n_padded, self.n_nvls, self.bucket, lr, momentum, dampening, weight_decay,
+            int(nesterov), int(first_step), _lib._stream(stream)), "nd_outer_sync_hybrid")
 
     def last_ms(self) -> float:
         ms = ctypes.c_float()
@@ -284,13 +290,22 @@ class NvlsContext:
         return float(ms.value)
 
     def gather_shards(self, shard: torch.Tensor) -> torch.Tensor:
-        """Collective: bucket-interleaved shards (rank r owns the r-th slice of every bucket) -> flat buffer."""
+        """Collective: this layout's shards -> flat buffer."""
         parts = [torch.empty_like(shard) for _ in range(self.world)]
         dist.all_gather(parts, shard, group=self.group)
         full = torch.empty(self.n_padded, dtype=shard.dtype, device=shard.device)
         for r, part in enumerate(parts):
-            full[shard_index_map(self.n_padded, self.world, r, self.bucket).to(shard.device)] = part
+            full[self.shard_indices(r).to(shard.device)] = part
         return full
+
+    def shard_indices(self, rank=None) -> torch.Tensor:
+        """Global element indices of rank's shard, in shard order: its slices of the in-switch region
+        (bucket-interleaved) followed by its contiguous piece of the peer-kernel region."""
+        r = self.rank if rank is None else rank
+        a = shard_index_map(self.n_nvls, self.world, r, self.bucket)
+        sB = (self.n_padded - self.n_nvls) // self.world
+        b = torch.arange(self.n_nvls + r * sB, self.n_nvls + (r + 1) * sB, dtype=torch.int64)
+        return torch.cat([a, b])
 
     def close(self) -> None:
         if getattr(self, "_h", None):

@@ -149,7 +149,7 @@ def _worker(rank, world, store, bucket_mb, mode, result_path):
 
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("mode,bucket_mb", [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_offload", 64.0),
-                                            ("p2p_bf16", 64.0), ("p2p_rep2", 64.0), ("nvls", 64.0), ("nvls", 0.002)])
+                                            ("p2p_bf16", 64.0), ("p2p_rep2", 64.0), ("nvls", 64.0), ("nvls", 0.002), ("hybrid", 0.002)])
 def test_sharded_outer_sync_vs_reference(world, mode, bucket_mb):
     if torch.cuda.device_count() < world:
         pytest.skip(f"needs {world} GPUs")
