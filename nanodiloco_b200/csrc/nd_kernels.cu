@@ -11,11 +11,16 @@
 // and table-driven multi-tensor forms of each for non-flat callers.
 //
 // Structure: an "Op" describes how to load / compute / store one group of four
-// consecutive elements (or one element on the scalar path).  Two drivers run an
-// Op: `flat_kernel` over one contiguous range and `table_kernel` over a device
-// table of tensors cut into ND_CHUNK-element chunks.  Both issue all loads of
-// kUnroll independent groups before any dependent arithmetic or store, so each
-// thread keeps kUnroll x (#inputs) 128-bit requests in flight.
+// consecutive elements (or one element on the scalar path).  Register-staged
+// drivers run an Op: `flat_kernel` over one contiguous range and `table_kernel`
+// over a device table of tensors cut into ND_CHUNK-element chunks.  Both issue
+// all loads of U independent groups before any dependent arithmetic or store,
+// so each thread keeps U x (#inputs) 128-bit requests in flight.
+// A "TileOp" wraps an Op for the TMA-staged driver (nd_tma.cuh: cp.async.bulk +
+// mbarrier, whole tiles landing in shared memory and leaving with bulk stores),
+// which is what the hot calls use whenever their buffers are 16-byte aligned:
+// fused outer kernel, shard update and AdamW.  The register-staged path serves
+// unaligned buffers, run-time worker counts, pseudo_grad, sumsq and the tables.
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>

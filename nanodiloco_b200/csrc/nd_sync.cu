@@ -1,4 +1,6 @@
-// nd_sync.cu -- the sharded multi-GPU outer sync (one process per GPU).
+// nd_sync.cu -- the multi-GPU outer sync as a bucketed NCCL pipeline (one process per GPU), and the
+// single-GPU outer step with a host-resident master copy.  (The peer-memory and in-switch variants,
+// which are faster on one NVSwitch node, live in nd_peer.cu.)
 //
 // Replaces the reference's per-tensor blocking `dist.all_reduce(AVG)` loop
 // (nanodiloco/diloco/diloco.py:46-50) and its outer optimizer step

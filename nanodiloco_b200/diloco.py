@@ -16,8 +16,10 @@ What changes underneath:
     once and never rebound (diloco.py:50 rebinds it each outer step);
   * the last-sync copy stays in HBM: the two PCIe crossings of diloco.py:29,47
     are gone;
-  * `outer_step` is one fused kernel at world size 1, and a bucketed
-    reduce-scatter -> fused update -> all-gather pipeline otherwise;
+  * `outer_step` is one fused kernel at world size 1; across GPUs it is one fused kernel per GPU
+    over NVLink peer memory (`sync="p2p"`, the default on one node), or a bucketed NCCL
+    reduce-scatter -> fused update -> all-gather pipeline (`"nccl"`), or an in-switch (NVLS
+    multicast) reduction (`"nvls"`, `"hybrid"`);
   * `inner_step` is a sum-of-squares pass plus one fused clip+AdamW pass, with
     the clip coefficient computed on the device (no host synchronisation).
 

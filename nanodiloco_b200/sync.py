@@ -33,6 +33,16 @@ def shard_index_map(n_padded: int, world: int, rank: int, bucket: int) -> torch.
     return torch.cat(parts) if parts else torch.zeros(0, dtype=torch.int64)
 
 
+def hybrid_index_map(n_padded: int, n_nvls: int, world: int, rank: int, bucket: int) -> torch.Tensor:
+    """Global element indices of `rank`'s shard under the hybrid layout (nd_outer_sync_hybrid): its slices
+    of the in-switch region [0, n_nvls) in bucket order, then its contiguous piece of the peer-kernel
+    region [n_nvls, n_padded).  Pure host logic (CPU tensor)."""
+    a = shard_index_map(n_nvls, world, rank, bucket)
+    sB = (n_padded - n_nvls) // world
+    b = torch.arange(n_nvls + rank * sB, n_nvls + (rank + 1) * sB, dtype=torch.int64)
+    return torch.cat([a, b])
+
+
 class SyncContext:
     def __init__(self, world: int, rank: int, *, bucket_elems: int, n_streams: int = 2, group=None,
                  device=None):
@@ -302,10 +312,7 @@ class NvlsContext:
         """Global element indices of rank's shard, in shard order: its slices of the in-switch region
         (bucket-interleaved) followed by its contiguous piece of the peer-kernel region."""
         r = self.rank if rank is None else rank
-        a = shard_index_map(self.n_nvls, self.world, r, self.bucket)
-        sB = (self.n_padded - self.n_nvls) // self.world
-        b = torch.arange(self.n_nvls + r * sB, self.n_nvls + (r + 1) * sB, dtype=torch.int64)
-        return torch.cat([a, b])
+        return hybrid_index_map(self.n_padded, self.n_nvls, self.world, r, self.bucket)
 
     def close(self) -> None:
         if getattr(self, "_h", None):

@@ -46,6 +46,18 @@ def test_shard_index_map_partitions_the_space(world, bucket, n):
     assert sizes == {n // world}
 
 
+@pytest.mark.parametrize("world,bucket,n,n_nvls", [(2, 8, 40, 24), (4, 32, 160, 96), (8, 64, 64 * 7, 64 * 3),
+                                                    (8, 64, 640, 0), (4, 16, 64, 64)])
+def test_hybrid_index_map_partitions_the_space(world, bucket, n, n_nvls):
+    from nanodiloco_b200.sync import hybrid_index_map
+    seen = torch.zeros(n, dtype=torch.int64)
+    for r in range(world):
+        idx = hybrid_index_map(n, n_nvls, world, r, bucket)
+        assert idx.numel() == n // world
+        seen[idx] += 1
+    assert torch.all(seen == 1)
+
+
 def test_cosine_schedule_matches_transformers():
     transformers = pytest.importorskip("transformers")
     a = torch.optim.AdamW([torch.nn.Parameter(torch.zeros(1))], lr=4e-4)
