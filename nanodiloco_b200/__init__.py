@@ -1,13 +1,18 @@
 """nanodiloco_b200 -- the DiLoCo outer-sync hot path of SJCaldwell/NanoDiloco on B200.
 
 `from nanodiloco_b200 import Diloco` is the drop-in for `from nanodiloco import Diloco`
-(reference nanodiloco/__init__.py:1-4).
+(reference nanodiloco/__init__.py:1-4).  Attributes resolve lazily so that
+`python -m nanodiloco_b200.build` does not import torch.
 """
-from .diloco import Diloco
-
 __all__ = ["Diloco", "main"]
 
 
-def main():
-    from .main import main as _main
-    return _main()
+def __getattr__(name):
+    if name == "Diloco":
+        from .diloco import Diloco
+        return Diloco
+    if name == "main":
+        from .main import main as fn
+        globals()["main"] = fn          # the submodule import bound the module under this name; rebind
+        return fn
+    raise AttributeError(f"module 'nanodiloco_b200' has no attribute {name!r}")
