@@ -278,3 +278,25 @@ def test_peer_context_world1_matches_oracle():
     ctx.barrier()                                                                # single-rank barrier returns
     torch.cuda.synchronize()
     ctx.close()
+
+
+def test_multi_tensor_forms_with_bf16_working_copy():
+    sizes = [128, 8, 16385, 40_000, 24]
+    L = _lib.load()
+    ms = [dev(_rand(s, 10 + i, 0.02)) for i, s in enumerate(sizes)]
+    ls = [(m + dev(_rand(s, 50 + i, 1e-3))).to(torch.bfloat16) for i, (m, s) in enumerate(zip(ms, sizes))]
+    bs = [dev(_rand(s, 90 + i, 1e-3)) for i, s in enumerate(sizes)]
+    pgs = [torch.empty_like(m) for m in ms]
+    tab, T, chunks = _lib.make_table(list(zip(ms, ls, pgs)), "cuda")
+    _lib.check(L.nd_pseudo_grad_mt(tab.data_ptr(), T, chunks, _lib.ND_BF16, _lib._stream()))
+    for m, l, pg in zip(ms, ls, pgs):
+        assert torch.equal(pg, m - l.float())
+    want = []
+    for m, l, b in zip(ms, ls, bs):
+        m2, l2, b2 = m.clone(), l.clone(), b.clone()
+        _lib.outer_fused(m2, b2, [l2], lr=LR, momentum=MU)
+        want.append((m2, b2, l2))
+    tab, T, chunks = _lib.make_table(list(zip(ms, bs, ls)), "cuda")
+    _lib.check(L.nd_outer_fused_mt(tab.data_ptr(), T, chunks, _lib.ND_BF16, LR, MU, 0.0, 0.0, 1, 0, _lib._stream()))
+    for (m2, b2, l2), m, l, b in zip(want, ms, ls, bs):
+        assert torch.equal(m, m2) and torch.equal(b, b2) and torch.equal(l, l2)
