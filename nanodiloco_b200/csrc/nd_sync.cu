@@ -39,8 +39,6 @@ struct NcclApi {
     int (*CommDestroy)(ncclComm_t) = nullptr;
     int (*ReduceScatter)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
-    int (*GroupStart)() = nullptr;
-    int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
 
@@ -67,8 +65,6 @@ static int load_nccl() {
     ND_SYM(CommDestroy, "ncclCommDestroy");
     ND_SYM(ReduceScatter, "ncclReduceScatter");
     ND_SYM(AllGather, "ncclAllGather");
-    ND_SYM(GroupStart, "ncclGroupStart");
-    ND_SYM(GroupEnd, "ncclGroupEnd");
     ND_SYM(GetErrorString, "ncclGetErrorString");
 #undef ND_SYM
     g_nccl.handle = h;

@@ -34,7 +34,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from .flat import FlatLayout, rehome_
+from .flat import FlatLayout, rehome_, trainable_runs
 
 
 def _cosine_schedule_with_warmup(optimizer, num_warmup_steps: int, num_training_steps: int):
@@ -265,25 +265,9 @@ class Diloco:
         return out
 
     def _trainable_runs(self, optimizer):
-        """(group, start, end) ranges covering maximal runs of consecutive TRAINABLE tensors of each
-        param group.  torch's AdamW never touches a parameter whose `.grad` is None -- which is what a
-        frozen (`requires_grad=False`) parameter has -- so frozen tensors must not even see weight decay;
-        they still take part in the outer sync (their pseudo-gradient is zero)."""
-        out, i = [], 0
-        for g in optimizer.param_groups:
-            run_start = None
-            for j, p in enumerate(g["params"]):
-                k = i + j
-                if p.requires_grad:
-                    if run_start is None:
-                        run_start = k
-                    last = k
-                if (not p.requires_grad or j == len(g["params"]) - 1) and run_start is not None:
-                    s, e = self.layout.span(run_start, last)
-                    out.append((g, s, e))
-                    run_start = None
-            i += len(g["params"])
-        return out
+        """(group, start, end) ranges of consecutive trainable tensors per param group (flat.trainable_runs)."""
+        groups = optimizer.param_groups
+        return [(groups[gi], s, e) for gi, s, e in trainable_runs(self.layout, [g["params"] for g in groups])]
 
     def _attach_grads(self) -> None:
         for p, gv in zip(self._params, self._grad_views):

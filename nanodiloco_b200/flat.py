@@ -61,3 +61,26 @@ def rehome_(params: Sequence[torch.nn.Parameter], flat: torch.Tensor, layout: Fl
         for p, v in zip(params, layout.views(flat)):
             v.copy_(p.data)
             p.data = v
+
+
+def trainable_runs(layout: FlatLayout, groups: Sequence[Sequence[torch.nn.Parameter]], first_index: int = 0):
+    """For each parameter group (a list of parameters laid out consecutively from tensor index
+    `first_index`), the maximal runs of consecutive TRAINABLE tensors as (group_index, start, end)
+    element ranges.  torch's optimizers never touch a parameter without a gradient -- which is what a
+    frozen (`requires_grad=False`) parameter has -- so the fused inner step must skip those tensors
+    entirely (not even weight decay); they still take part in the outer sync."""
+    out, i = [], first_index
+    for gi, params in enumerate(groups):
+        run_start = last = None
+        for j, p in enumerate(params):
+            k = i + j
+            if p.requires_grad:
+                if run_start is None:
+                    run_start = k
+                last = k
+            if (not p.requires_grad or j == len(params) - 1) and run_start is not None:
+                s, e = layout.span(run_start, last)
+                out.append((gi, s, e))
+                run_start = None
+        i += len(params)
+    return out

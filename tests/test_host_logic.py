@@ -58,6 +58,21 @@ def test_hybrid_index_map_partitions_the_space(world, bucket, n, n_nvls):
     assert torch.all(seen == 1)
 
 
+def test_trainable_runs_skip_frozen_tensors():
+    from nanodiloco_b200.flat import trainable_runs
+    ps = [torch.nn.Parameter(torch.zeros(n)) for n in (8, 5, 16, 4, 12, 7)]
+    ps[1].requires_grad_(False)
+    ps[5].requires_grad_(False)
+    lay = FlatLayout.plan(ps)
+    runs = trainable_runs(lay, [ps[:4], ps[4:]])
+    # group 0: tensor 0 alone, then tensors 2..3; group 1: tensor 4 alone
+    assert runs == [(0, lay.offsets[0], lay.offsets[0] + 8), (0, lay.offsets[2], lay.offsets[3] + 4),
+                    (1, lay.offsets[4], lay.offsets[4] + 12)]
+    for p in ps:
+        p.requires_grad_(True)
+    assert trainable_runs(lay, [ps]) == [(0, 0, lay.offsets[5] + 7)]
+
+
 def test_cosine_schedule_matches_transformers():
     transformers = pytest.importorskip("transformers")
     a = torch.optim.AdamW([torch.nn.Parameter(torch.zeros(1))], lr=4e-4)
