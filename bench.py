@@ -519,6 +519,17 @@ def native_arm(args):
     step_roof["t_nvlink_ms_at_770_measured_peer_copy"] = nvl_bytes / 770e9 * 1e3
     step_roof["frac_of_bound_at_770"] = max(step_roof["t_hbm_ms"], nvl_bytes / 770e9 * 1e3) / ms
     step_roof["sync"] = mode
+    if world > 1 and mode in ("p2p", "nvls", "hybrid"):
+        # A fused compute+exchange step is bounded by the slower of its HBM time and its NVLink time; at
+        # W >= 2 that is NVLink.  Denominator: the measured peer-copy bandwidth of this pool, 770 GB/s per
+        # direction per GPU (B200_PROFILING.md; 900 nominal -- that fraction is in step_roofline).
+        nvl_gbs = nvl_bytes / (ms * 1e-3) / 1e9
+        roofline = {"bound": "nvlink", "achieved": nvl_gbs, "peak": 770.0, "unit": "GB/s", "frac": nvl_gbs / 770.0,
+                    "traffic": None, "kernel": kern_name,
+                    "peak_source": "measured peer copy per direction per GPU (B200_PROFILING.md); 900 GB/s nominal",
+                    "algorithmic_bytes_per_launch": nvl_bytes, "kernel_ms": ms,
+                    "hbm": {"achieved": achieved, "peak": peak, "frac": achieved / peak, "peak_source": peak_src,
+                            "algorithmic_bytes_per_launch": kern_bytes}}
 
     # ---- e2e: last-sync copy in pinned HOST memory, H2D + D2H inside the timed region ------------
     e2e = None
