@@ -29,3 +29,37 @@ def test_native_arm_refuses_to_run_without_a_gpu():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1"],
                          capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert out.returncode != 0 and "no CUDA device" in (out.stderr + out.stdout)
+
+
+def _bench_module():
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def test_cpu_sample_is_a_bounded_prefix_of_the_tensor_list():
+    b = _bench_module()
+    shapes = b.workload_shapes("llama1b")
+    assert len(shapes) == 201 and sum(b.numel(s) for s in shapes) == 1_261_529_088
+    sample, n = b.cpu_sample_shapes(shapes, 256_000_000)
+    assert sample == shapes[:len(sample)] and n <= 256_000_000 and n > 100_000_000
+    one, n1 = b.cpu_sample_shapes(shapes, 1)            # never empty: at least the first tensor
+    assert len(one) == 1 and n1 == 32000 * 2048
+
+
+def test_workload_config_names_the_workload():
+    import argparse
+    b = _bench_module()
+    cfg = b.workload_config(argparse.Namespace(workload="llama1b", replicas=2, dtype="bf16"), 1_261_529_088, 201, 8)
+    assert "llama1b" in cfg["workload"] and "4 worker(s), 2 GPU(s) per worker" in cfg["workload"]
+    assert cfg["parallelism"] == "diloco-dp4x2" and "model" not in cfg
+
+
+def test_clock_sampler_degrades_without_nvml():
+    b = _bench_module()
+    s = b.ClockSampler(0)
+    s.start(); s.stop(); s.close()
+    out = s.summary()
+    assert set(out) >= {"sm_mhz", "sm_max_mhz", "reasons"}
