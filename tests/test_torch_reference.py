@@ -124,3 +124,21 @@ def test_shape_table_matches_the_real_model():
     got = [tuple(p.shape) for p in model.parameters()]
     assert sorted(got) == sorted(llama_shapes(**CONFIGS["tiny"]))
     assert sum(int(np.prod(s)) for s in got) == 9_766_528
+
+
+@pytest.mark.skipif(not os.path.exists(REF), reason="the reference is only mounted in the build container")
+@pytest.mark.parametrize("W", [1, 2])
+def test_committed_fixtures_regenerate_bit_for_bit_from_the_reference(tmp_path, W):
+    """tests/golden/*.npz are outputs of the reference itself: re-run the generator (which drives the
+    reference's own `Diloco` class under gloo) and compare with the committed files."""
+    import sys
+    import torch.multiprocessing as mp
+    here = os.path.dirname(os.path.abspath(__file__))
+    sys.path.insert(0, os.path.join(here, "golden"))    # spawned workers import the generator by name
+    import make_golden as mg
+    out = str(tmp_path / f"outer_w{W}.npz")
+    mp.spawn(mg.outer_worker, args=(W, str(tmp_path / "store"), out), nprocs=W, join=True)
+    fresh, kept = np.load(out), np.load(os.path.join(here, "golden", f"outer_w{W}.npz"))
+    assert sorted(fresh.files) == sorted(kept.files)
+    for k in kept.files:
+        assert np.array_equal(fresh[k], kept[k]), k
