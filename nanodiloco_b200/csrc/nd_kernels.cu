@@ -25,6 +25,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <cmath>
+#include <atomic>
 
 #include "nd_common.cuh"
 #include "nd_error.h"
@@ -384,10 +385,13 @@ struct FusedTileOp {
     __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
 };
 
-// buffers: 0 = master shard, 1 = momentum shard, 2 = reduced pseudo-gradient (reused for the bf16 copy-back)
+// buffers: 0 = master shard, 1 = momentum shard, 2 = reduced pseudo-gradient, 3 = bf16 image of the
+// new parameters (bf16 working copy only).  The image cannot share buffer 2: a thread's bf16 store
+// at bytes [2i, 2i+8) would land on fp32 pseudo-gradient elements that another warp has yet to read.
 template <bool BF16, bool SUM>
 struct ShardTileOp {
-    static constexpr int kBufs = 3;
+    static constexpr int kBufs = BF16 ? 4 : 3;
+    static constexpr int kOutBuf = BF16 ? 3 : 0;
     static constexpr bool kHasSum = SUM;
     static constexpr int kEsz = BF16 ? 2 : 4;
     static constexpr int kGran = 16 / kEsz;
@@ -410,7 +414,7 @@ struct ShardTileOp {
             o.one(p.x, b.x, g.x); o.one(p.y, b.y, g.y); o.one(p.z, b.z, g.z); o.one(p.w, b.w, g.w);
             sts4(st.buf(0) + i, p);
             sts4(st.buf(1) + i, b);
-            if (BF16) sts_bf16x4(st.buf(2), i, p);
+            if (BF16 && o.local_out) sts_bf16x4(st.buf(kOutBuf), i, p);
         }
     }
     template <int TILE>
@@ -418,7 +422,7 @@ struct ShardTileOp {
         tma::bulk_store(o.master + off, st.buf(0), (uint32_t)len * 4);
         tma::bulk_store(o.mom + off, st.buf(1), (uint32_t)len * 4);
         if (o.local_out)
-            tma::bulk_store(static_cast<char*>(o.local_out) + off * kEsz, st.buf(BF16 ? 2 : 0), (uint32_t)len * kEsz);
+            tma::bulk_store(static_cast<char*>(o.local_out) + off * kEsz, st.buf(kOutBuf), (uint32_t)len * kEsz);
     }
     __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
 };
@@ -544,17 +548,17 @@ __global__ void __launch_bounds__(kThreads, MINB) table_kernel(Op op, const nd_t
 // Host side
 // ===========================================================================
 
-static int g_sm_count[64];
+static std::atomic<int> g_sm_count[64];
 
 static int sm_count() {
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
-    if (g_sm_count[dev] == 0) {
-        int n = 0;
+    int n = g_sm_count[dev].load(std::memory_order_relaxed);
+    if (n == 0) {
         if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-        g_sm_count[dev] = n;
+        g_sm_count[dev].store(n, std::memory_order_relaxed);
     }
-    return g_sm_count[dev];
+    return n;
 }
 
 // grid: every SM gets MINB resident CTAs (one full wave); never more CTAs than work.
@@ -594,13 +598,13 @@ static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_ou
     auto kernel = tma::tile_kernel<TILE, STAGES, THREADS, MINB, TileOp>;
     constexpr size_t smem = (size_t)STAGES * TileOp::kBufs * TILE * sizeof(float);
     static_assert(smem <= 227 * 1024, "stage set exceeds the 227 KB of shared memory a CTA can have");
-    static bool configured[64] = {false};
+    static std::atomic<bool> configured[64];   // per device; two threads racing here both set the same attribute
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
-    if (!configured[dev]) {
+    if (!configured[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return set_error(ND_ECUDA, "cudaFuncSetAttribute(smem=%zu): %s", smem, cudaGetErrorString(e));
-        configured[dev] = true;
+        configured[dev].store(true, std::memory_order_release);
     }
     const int64_t ntiles = ((n & ~(int64_t)(TileOp::kGran - 1)) + TILE - 1) / TILE;
     int64_t full = (int64_t)sm_count() * MINB;
@@ -651,6 +655,7 @@ constexpr int U_ADAM = 1, B_ADAM = 2;
 #define ND_TILE_FUSED4 1024, 3, 256, 3
 #define ND_TILE_FUSED8 1024, 3, 256, 1
 #define ND_TILE_SHARD 4096, 2, 512, 2
+#define ND_TILE_SHARD_BF16 2048, 2, 512, 2   // four buffers per stage: 64 KB per CTA
 #define ND_TILE_ADAM 2048, 2, 512, 2
 
 template <int W, bool BF16, bool SUM>
@@ -764,7 +769,8 @@ int nd_outer_nesterov(float* master, float* mom, const float* pg_sum, void* loca
         op.world = world; op.h = h; op.acc = 0.f;                                            \
         if (aligned16(master) && aligned16(mom) && aligned16(pg_sum) && aligned16(local_out)) { \
             ShardTileOp<BF, SM> t{op};                                                       \
-            return launch_tile<ND_TILE_SHARD>(t, n, scratch, sumsq_out, s);                  \
+            if constexpr (BF) return launch_tile<ND_TILE_SHARD_BF16>(t, n, scratch, sumsq_out, s); \
+            else return launch_tile<ND_TILE_SHARD>(t, n, scratch, sumsq_out, s);             \
         }                                                                                    \
         return launch_flat<U_SHARD, B_SHARD>(op, n, scratch, sumsq_out, s);                  \
     } while (0)
@@ -857,8 +863,10 @@ static_assert(sizeof(Scratch) <= ND_SUMSQ_STATIC_SCRATCH_BYTES, "static scratch 
 
 // In host code `g_sumsq_static_scratch` is only a handle for the runtime, not a device address:
 // the address a kernel can use comes from cudaGetSymbolAddress, looked up once per device with
-// that device current.
-static void* g_sumsq_static_ptr[64];
+// that device current.  The cache is atomic so that two host threads making their first call on a
+// device at the same time is not a data race (both would store the same address).  It does not
+// survive cudaDeviceReset: a process that resets a device must not call this entry point afterwards.
+static std::atomic<void*> g_sumsq_static_ptr[64];
 
 int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t stream) {
     ND_REQUIRE(n >= 0, "n < 0");
@@ -871,14 +879,14 @@ int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t
     int dev = 0;
     ND_CUDA(cudaGetDevice(&dev));
     if (dev < 0 || dev >= 64) return set_error(ND_EINVAL, "nd_sumsq_static: device index %d out of range", dev);
-    if (!g_sumsq_static_ptr[dev]) {  // set-up: first call on this device
-        void* p = nullptr;
-        cudaError_t e = cudaGetSymbolAddress(&p, g_sumsq_static_scratch);
-        if (e != cudaSuccess || !p)
+    void* sptr = g_sumsq_static_ptr[dev].load(std::memory_order_acquire);
+    if (!sptr) {  // set-up: first call on this device
+        cudaError_t e = cudaGetSymbolAddress(&sptr, g_sumsq_static_scratch);
+        if (e != cudaSuccess || !sptr)
             return set_error(ND_ECUDA, "nd_sumsq_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e));
-        g_sumsq_static_ptr[dev] = p;
+        g_sumsq_static_ptr[dev].store(sptr, std::memory_order_release);
     }
-    Scratch* sc = static_cast<Scratch*>(g_sumsq_static_ptr[dev]);
+    Scratch* sc = static_cast<Scratch*>(sptr);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
     // the array keeps whatever the previous call (or a call that died half-way) left behind: the
     // arrival counter is the one field that must be zero when the kernel starts

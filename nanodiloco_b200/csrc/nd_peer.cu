@@ -25,10 +25,22 @@ namespace nd {
 
 constexpr size_t kFlagBytes = 4096;  // per-rank flag page appended to the shared buffer
 
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // Barrier across the ranks of a node: thread w publishes `epoch` to slot [rank] of rank w's flag
-// page, then waits until slot [w] of our own page reaches `epoch`.  System-scope release/acquire;
-// bounded wait (~10 s of SM clock) so that a dead peer traps this rank instead of hanging the box.
-__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int rank, uint32_t epoch, int channel) {
+// page, then waits until slot [w] of our own page reaches `epoch`.  System-scope release/acquire.
+// The first barrier of an outer step absorbs the skew between workers (a rank that checkpoints,
+// evaluates or stalls on its data loader arrives late), so the wait is bounded by `timeout_ns` of
+// wall time -- ND_PEER_TIMEOUT_S, default 1800 s, 0 = wait for ever -- not by a few seconds.  When
+// it does expire the waiting rank records WHO it was waiting for in `diag` (page-locked host memory
+// the host can still read after the context is lost; nd_last_error / nd_peer_last_ms report it)
+// and traps, rather than going on to average parameters that are not there.
+__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int rank, uint32_t epoch, int channel,
+                                    unsigned long long timeout_ns, int* diag) {
     const int w = threadIdx.x;
     if (w >= world) return;
     __threadfence_system();
@@ -37,12 +49,16 @@ __global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int 
     uint32_t* remote = flag_pages[w] + channel * ND_MAX_WORKERS + rank;
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
     const uint32_t* mine = flag_pages[rank] + channel * ND_MAX_WORKERS + w;
-    const long long t0 = clock64();
-    for (;;) {
+    const unsigned long long t0 = global_ns();
+    for (unsigned spins = 0;; ++spins) {
         uint32_t v;
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
         if ((int32_t)(v - epoch) >= 0) break;
-        if (clock64() - t0 > 20000000000LL) __trap();
+        if (timeout_ns && (spins & 1023u) == 1023u && global_ns() - t0 > timeout_ns) {
+            if (diag) { diag[1] = w; diag[2] = channel; diag[3] = (int)epoch; __threadfence_system(); diag[0] = 1; }
+            __threadfence_system();
+            __trap();
+        }
     }
     __threadfence_system();
 }
@@ -118,9 +134,46 @@ struct nd_peer_ctx {
     cudaEvent_t done[kStreams] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t fork = nullptr;
     std::vector<cudaEvent_t> bucket_events;  // NVLS pipeline: two per bucket
+    unsigned long long timeout_ns = 0;       // bound on a flag wait (0 = none); ND_PEER_TIMEOUT_S
+    int* diag_host = nullptr;                // page-locked, device-mapped: {timed_out, waited_for_rank, channel, epoch}
+    int* diag_dev = nullptr;
 };
 
+static unsigned long long peer_timeout_ns() {
+    const char* e = getenv("ND_PEER_TIMEOUT_S");
+    const double s = e ? atof(e) : 1800.0;
+    return s <= 0.0 ? 0ull : (unsigned long long)(s * 1e9);
+}
+
+// what the two constructors share once `base` is filled in; on failure the caller destroys the context
+static int peer_ctx_finish(nd_peer_ctx* c) {
+    std::vector<uint32_t*> pages(c->world);
+    for (int w = 0; w < c->world; ++w)
+        pages[w] = reinterpret_cast<uint32_t*>(static_cast<char*>(c->base[w]) + c->bytes);
+    ND_CUDA(cudaMalloc(&c->flag_pages_dev, sizeof(uint32_t*) * c->world));
+    ND_CUDA(cudaMemcpy(c->flag_pages_dev, pages.data(), sizeof(uint32_t*) * c->world, cudaMemcpyHostToDevice));
+    ND_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&c->diag_host), 4 * sizeof(int), cudaHostAllocMapped));
+    memset(c->diag_host, 0, 4 * sizeof(int));
+    ND_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->diag_dev), c->diag_host, 0));
+    c->timeout_ns = peer_timeout_ns();
+    ND_CUDA(cudaEventCreate(&c->t0));
+    ND_CUDA(cudaEventCreate(&c->t1));
+    return ND_OK;
+}
+
+// A flag wait that expired left a note in page-locked memory before it trapped: turn the opaque
+// "unspecified launch failure" the next CUDA call reports into something a user can act on.
+static int peer_diag(const nd_peer_ctx* c, const char* where) {
+    if (c && c->diag_host && c->diag_host[0])
+        return set_error(ND_ESTATE, "%s: rank %d waited longer than ND_PEER_TIMEOUT_S for rank %d (flag channel %d, "
+                         "epoch %d); the CUDA context of this process is lost", where, c->rank, c->diag_host[1],
+                         c->diag_host[2], c->diag_host[3]);
+    return ND_OK;
+}
+
 extern "C" {
+
+int nd_peer_ctx_destroy(nd_peer_ctx* c);
 
 int nd_peer_alloc(size_t bytes, void** dev_ptr_out, char handle_out[ND_IPC_HANDLE_BYTES]) {
     if (!dev_ptr_out || !handle_out || bytes == 0) return set_error(ND_EINVAL, "nd_peer_alloc: bad argument");
@@ -163,19 +216,16 @@ int nd_peer_ctx_create(int world, int rank, void* my_buffer, size_t bytes, const
         memcpy(&h, handles_host + (size_t)w * ND_IPC_HANDLE_BYTES, ND_IPC_HANDLE_BYTES);
         cudaError_t e = cudaIpcOpenMemHandle(&c->base[w], h, cudaIpcMemLazyEnablePeerAccess);
         if (e != cudaSuccess) {
-            for (int v = 0; v < w; ++v)
-                if (v != rank && c->base[v]) cudaIpcCloseMemHandle(c->base[v]);
-            delete c;
+            c->base[w] = nullptr;
+            nd_peer_ctx_destroy(c);      // closes the mappings opened so far
             return set_error(ND_ECUDA, "cudaIpcOpenMemHandle(rank %d) failed: %s (is peer access available?)", w,
                              cudaGetErrorString(e));
         }
     }
-    std::vector<uint32_t*> pages(world);
-    for (int w = 0; w < world; ++w) pages[w] = reinterpret_cast<uint32_t*>(static_cast<char*>(c->base[w]) + c->bytes);
-    ND_CUDA(cudaMalloc(&c->flag_pages_dev, sizeof(uint32_t*) * world));
-    ND_CUDA(cudaMemcpy(c->flag_pages_dev, pages.data(), sizeof(uint32_t*) * world, cudaMemcpyHostToDevice));
-    ND_CUDA(cudaEventCreate(&c->t0));
-    ND_CUDA(cudaEventCreate(&c->t1));
+    if (int rc = peer_ctx_finish(c)) {   // nd_last_error() keeps the message of the call that failed
+        nd_peer_ctx_destroy(c);
+        return rc;
+    }
     *out = c;
     return ND_OK;
 }
@@ -192,12 +242,10 @@ int nd_peer_ctx_create_from_ptrs(int world, int rank, void* const* bases_host, s
     c->world = world; c->rank = rank; c->bytes = (bytes + 255) / 256 * 256;
     c->owns_mappings = false;
     c->base.assign(bases_host, bases_host + world);
-    std::vector<uint32_t*> pages(world);
-    for (int w = 0; w < world; ++w) pages[w] = reinterpret_cast<uint32_t*>(static_cast<char*>(c->base[w]) + c->bytes);
-    ND_CUDA(cudaMalloc(&c->flag_pages_dev, sizeof(uint32_t*) * world));
-    ND_CUDA(cudaMemcpy(c->flag_pages_dev, pages.data(), sizeof(uint32_t*) * world, cudaMemcpyHostToDevice));
-    ND_CUDA(cudaEventCreate(&c->t0));
-    ND_CUDA(cudaEventCreate(&c->t1));
+    if (int rc = peer_ctx_finish(c)) {
+        nd_peer_ctx_destroy(c);
+        return rc;
+    }
     *out = c;
     return ND_OK;
 }
@@ -214,6 +262,7 @@ int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     if (c->fork) cudaEventDestroy(c->fork);
     for (auto e : c->bucket_events) cudaEventDestroy(e);
     if (c->flag_pages_dev) cudaFree(c->flag_pages_dev);
+    if (c->diag_host) cudaFreeHost(c->diag_host);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     delete c;
@@ -245,7 +294,8 @@ static int fill_rw(const nd_peer_ctx* c, size_t byte_off, void** reads, void** w
 
 static int peer_barrier_ch(nd_peer_ctx* c, int channel, cudaStream_t stream) {
     c->epoch[channel] += 1;
-    peer_barrier_kernel<<<1, 32, 0, stream>>>(c->flag_pages_dev, c->world, c->rank, c->epoch[channel], channel);
+    peer_barrier_kernel<<<1, 32, 0, stream>>>(c->flag_pages_dev, c->world, c->rank, c->epoch[channel], channel,
+                                              c->timeout_ns, c->diag_dev);
     return check_launch("peer_barrier_kernel");
 }
 
@@ -375,16 +425,16 @@ static int nvls_launch(nd_peer_ctx* c, float* master, float* mom, const float* m
 int nd_outer_sync_hybrid(nd_peer_ctx* c, float* local, float* pg, float* mc_local, float* mc_pg, float* master,
                          float* mom_shard, int64_t n_padded, int64_t n_nvls, int64_t bucket_elems, float lr, float mu,
                          float dampening, float wd, int nesterov, int first_step, nd_stream_t stream_) {
-    if (!c) return set_error(ND_ESTATE, "nd_outer_sync_nvls: null context");
+    if (!c) return set_error(ND_ESTATE, "nd_outer_sync_hybrid: null context");
     const int W = c->world;
-    if (c->replicas != 1) return set_error(ND_ESTATE, "nd_outer_sync_nvls: replicas are not supported");
+    if (c->replicas != 1) return set_error(ND_ESTATE, "nd_outer_sync_hybrid: replicas are not supported");
     const int64_t q = 4 * (int64_t)W;
     if (n_padded < 0 || n_padded % q != 0)
-        return set_error(ND_EINVAL, "nd_outer_sync_nvls: n_padded must be a multiple of 4*world");
-    if ((size_t)n_padded * 4 > c->bytes) return set_error(ND_EINVAL, "nd_outer_sync_nvls: n_padded exceeds the buffers");
+        return set_error(ND_EINVAL, "nd_outer_sync_hybrid: n_padded must be a multiple of 4*world");
+    if ((size_t)n_padded * 4 > c->bytes) return set_error(ND_EINVAL, "nd_outer_sync_hybrid: n_padded exceeds the buffers");
     if (n_padded && (!local || !pg || !mc_local || !mc_pg || !master || !mom_shard))
-        return set_error(ND_EINVAL, "nd_outer_sync_nvls: null pointer");
-    if (bucket_elems < 1) return set_error(ND_EINVAL, "nd_outer_sync_nvls: bucket_elems < 1");
+        return set_error(ND_EINVAL, "nd_outer_sync_hybrid: null pointer");
+    if (bucket_elems < 1) return set_error(ND_EINVAL, "nd_outer_sync_hybrid: bucket_elems < 1");
     if (n_nvls < 0 || n_nvls > n_padded || n_nvls % q != 0)
         return set_error(ND_EINVAL, "nd_outer_sync_hybrid: n_nvls must be a multiple of 4*world in [0, n_padded]");
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
@@ -470,7 +520,11 @@ int nd_outer_sync_nvls(nd_peer_ctx* c, float* local, float* pg, float* mc_local,
 int nd_peer_last_ms(nd_peer_ctx* c, float* ms_out) {
     if (!c || !ms_out) return set_error(ND_EINVAL, "nd_peer_last_ms: null argument");
     if (!c->timed) return set_error(ND_ESTATE, "nd_peer_last_ms: no nd_outer_sync_p2p has run");
-    ND_CUDA(cudaEventSynchronize(c->t1));
+    cudaError_t es = cudaEventSynchronize(c->t1);
+    if (es != cudaSuccess) {
+        if (int rc = peer_diag(c, "nd_peer_last_ms")) return rc;
+        return set_error(ND_ECUDA, "nd_peer_last_ms: cudaEventSynchronize failed: %s", cudaGetErrorString(es));
+    }
     ND_CUDA(cudaEventElapsedTime(ms_out, c->t0, c->t1));
     return ND_OK;
 }

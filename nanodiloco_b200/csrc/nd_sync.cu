@@ -93,7 +93,22 @@ struct nd_sync_ctx {
     bool timed = false;
 };
 
+static int sync_ctx_streams(nd_sync_ctx* c) {
+    c->streams.assign(c->n_streams, nullptr);
+    c->done.assign(c->n_streams, nullptr);
+    for (int i = 0; i < c->n_streams; ++i) {
+        ND_CUDA(cudaStreamCreateWithFlags(&c->streams[i], cudaStreamNonBlocking));
+        ND_CUDA(cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming));
+    }
+    ND_CUDA(cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming));
+    ND_CUDA(cudaEventCreate(&c->t0));
+    ND_CUDA(cudaEventCreate(&c->t1));
+    return ND_OK;
+}
+
 extern "C" {
+
+int nd_sync_ctx_destroy(nd_sync_ctx* c);
 
 int nd_nccl_unique_id(char out_host[ND_UNIQUE_ID_BYTES]) {
     if (!out_host) return set_error(ND_EINVAL, "nd_nccl_unique_id: null output");
@@ -130,23 +145,18 @@ int nd_sync_ctx_create(const char unique_id_host[ND_UNIQUE_ID_BYTES], int world,
             return set_error(ND_ENCCL, "ncclCommInitRank failed: %s", g_nccl.GetErrorString(r));
         }
     }
-    c->streams.resize(n_streams);
-    c->done.resize(n_streams);
-    for (int i = 0; i < n_streams; ++i) {
-        ND_CUDA(cudaStreamCreateWithFlags(&c->streams[i], cudaStreamNonBlocking));
-        ND_CUDA(cudaEventCreateWithFlags(&c->done[i], cudaEventDisableTiming));
+    if (int rc = sync_ctx_streams(c)) {   // streams, events: on failure release whatever exists so far
+        nd_sync_ctx_destroy(c);
+        return rc;
     }
-    ND_CUDA(cudaEventCreateWithFlags(&c->fork, cudaEventDisableTiming));
-    ND_CUDA(cudaEventCreate(&c->t0));
-    ND_CUDA(cudaEventCreate(&c->t1));
     *out = c;
     return ND_OK;
 }
 
 int nd_sync_ctx_destroy(nd_sync_ctx* c) {
     if (!c) return ND_OK;
-    for (auto s : c->streams) cudaStreamDestroy(s);
-    for (auto e : c->done) cudaEventDestroy(e);
+    for (auto s : c->streams) if (s) cudaStreamDestroy(s);
+    for (auto e : c->done) if (e) cudaEventDestroy(e);
     if (c->fork) cudaEventDestroy(c->fork);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);

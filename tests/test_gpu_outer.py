@@ -160,6 +160,39 @@ def test_outer_nesterov_shard(W, with_copy):
         assert torch.equal(out, master)
 
 
+@pytest.mark.parametrize("first", [True, False])
+def test_outer_nesterov_shard_bf16_copy_back_tma_path(first):
+    """bf16 copy-back of the shard update on the TMA-staged path (every buffer 16-byte aligned), several
+    tiles per CTA, repeated: the bf16 image of the new parameters has a stage buffer of its own -- when
+    it shared the pseudo-gradient's, one warp's store could overwrite elements another warp had yet to
+    read, and only some runs would show it."""
+    n = 148 * 2 * 2048 * 3 + 8 * 37            # > 2 tiles for every CTA of a full grid, plus a partial tile
+    W = 4
+    master_np, mom_np = _rand(n, 1, 0.02), _rand(n, 2, 1e-3)
+    locs_np = [master_np + _rand(n, 10 + w, 1e-3) for w in range(W)]
+    pg_sum = O.pseudo_grad(master_np, locs_np[0])
+    for l in locs_np[1:]:
+        pg_sum = (pg_sum + O.pseudo_grad(master_np, l)).astype(np.float32)
+    want_m, want_b = master_np.copy(), mom_np.copy()
+    O.outer_step(want_m, locs_np, want_b, lr=LR, momentum=MU, first_step=first)
+    want16 = torch.from_numpy(want_m).to(torch.bfloat16)
+    pg = dev(pg_sum)
+    for _ in range(20):
+        master, mom = dev(master_np), dev(mom_np)
+        out = torch.zeros(n, device="cuda", dtype=torch.bfloat16)
+        assert out.data_ptr() % 16 == 0 and master.data_ptr() % 16 == 0
+        _lib.outer_nesterov(master, mom, pg, out, world=float(W), lr=LR, momentum=MU, first_step=first)
+        assert np.array_equal(host(master), want_m) and np.array_equal(host(mom), want_b)
+        assert torch.equal(out.cpu(), want16)
+    # no copy-back requested: master and momentum only
+    master, mom = dev(master_np), dev(mom_np)
+    L = _lib.load()
+    rc = L.nd_outer_nesterov(master.data_ptr(), mom.data_ptr(), pg.data_ptr(), None, _lib.ND_BF16, n, float(W), LR, MU,
+                             0.0, 0.0, 1, int(first), None, None, torch.cuda.current_stream().cuda_stream)
+    assert rc == 0, L.nd_last_error()
+    assert np.array_equal(host(master), want_m) and np.array_equal(host(mom), want_b)
+
+
 # ---- multi-tensor forms --------------------------------------------------------------------------
 
 def test_multi_tensor_forms_match_flat():

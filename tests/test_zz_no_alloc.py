@@ -12,6 +12,7 @@ import pytest
 import torch
 
 from nanodiloco_b200 import _lib
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 
@@ -39,6 +40,9 @@ def test_static_scratch_matches_caller_scratch_twice_in_a_row():
     # same tolerance as the other sum-of-squares tests (tests/test_gpu_inner.py)
     assert got[0].item() == pytest.approx(want[0].item(), rel=2e-6)
     assert got[1].item() == pytest.approx(want[1].item(), rel=2e-6)
+    # and against the CPU oracle, so that this file does not only compare the kernel with itself
+    assert got[0].item() == pytest.approx(O.sumsq(a.cpu().numpy()), rel=2e-6)
+    assert got[1].item() == pytest.approx(O.sumsq(b.cpu().numpy()), rel=2e-6)
     # and again, now that the array holds the second call's partial sums
     again = torch.zeros(1, device="cuda")
     _sumsq_static(a, again)
