@@ -169,55 +169,98 @@ def cpu_sample_shapes(all_shapes, budget_elems: int):
     return out, tot
 
 
-def run_cpu_baseline(all_shapes, n_total: int, world: int, steps: int, warmup: int, budget_s: float):
+def mem_available_bytes() -> int:
+    try:
+        for line in open("/proc/meminfo"):
+            if line.startswith("MemAvailable:"):
+                return int(line.split()[1]) * 1024
+    except Exception:  # noqa: BLE001
+        pass
+    return 0
+
+
+# host bytes one CPU worker of the reference's path holds per parameter: parameters, the last-sync
+# snapshot, the pseudo-gradient, the momentum buffer and the clone of diloco.py:54 in flight
+CPU_BYTES_PER_PARAM = 5 * 4 + 2
+
+
+def run_cpu_baseline(all_shapes, n_total: int, world: int, steps: int, warmup: int, max_elems=None):
+    """The reference's CPU path (the port in oracle/torch_reference.py) on the WHOLE tensor list when the
+    host has the memory for `world` workers of it, else on the largest prefix that fits -- and then the
+    value reported is the prefix's own time, never a scaled one (`extrapolated` says so)."""
     cores = host_cores()
-    # calibrate on a small prefix, then size the sample so that (steps+warmup) fits the budget
-    calib, calib_n = cpu_sample_shapes(all_shapes[1:], 30_000_000)   # a few layer tensors
-    t = min(time_reference_cpu(calib, world, 1, 1, cores))
-    per_elem = t / max(1, calib_n)
-    budget_elems = int(budget_s / max(1e-12, per_elem * (steps + warmup)))
-    # bounded sample: at most ~256M params (memory: ~6 fp32 copies live at once on the host)
-    shapes, sample_n = cpu_sample_shapes(all_shapes, min(max(budget_elems, 2_000_000), 256_000_000))
+    avail = mem_available_bytes()
+    fit_elems = int(0.8 * avail / (CPU_BYTES_PER_PARAM * max(1, world))) if avail else n_total
+    budget = min(n_total, fit_elems, max_elems or n_total)
+    shapes, sample_n = (all_shapes, n_total) if budget >= n_total else cpu_sample_shapes(all_shapes, budget)
     times = time_reference_cpu(shapes, world, steps, warmup, cores)
     sec = statistics.median(times)
-    scale = n_total / sample_n
+    whole = sample_n == n_total
+    what = (f"oracle/torch_reference.py (statement-by-statement torch-CPU port of the reference's Diloco.outer_step, "
+            f"{'gloo W=%d' % world if world > 1 else 'W=1'}) on "
+            + (f"the whole model ({len(shapes)} tensors, {sample_n} params per worker)" if whole else
+               f"the first {len(shapes)} tensors = {sample_n} of {n_total} params per worker (host memory: "
+               f"{avail / 2**30:.0f} GiB available for {world} workers x {CPU_BYTES_PER_PARAM} B/param); the value is "
+               f"this sample's own time, NOT scaled to the full model")
+            + f"; median of {steps} steps after {warmup} warm-up; torch threads = {cores} in total")
     return {
-        "value": sec * 1e3 * scale, "unit": UNIT, "cores": cores, "kind": "port",
-        "sample": (f"oracle/torch_reference.py (statement-by-statement torch-CPU port of the reference's "
-                   f"Diloco.outer_step, {'gloo W=%d' % world if world > 1 else 'W=1'}) on the first {len(shapes)} "
-                   f"tensors = {sample_n} of {n_total} params; median of {steps} steps = {sec * 1e3:.1f} ms, "
-                   f"scaled x{scale:.2f} to the full model; torch threads = {cores}"),
-        "sample_ms": sec * 1e3, "sample_elems": sample_n,
+        "value": sec * 1e3, "unit": UNIT, "cores": cores, "kind": "port", "sample": what,
+        "sample_elems": sample_n, "full_elems": n_total, "extrapolated": False, "whole_workload": whole,
+        "best_ms": min(times) * 1e3, "steps_timed": len(times),
     }
 
 
 def _extras_n1(torch, _lib, dev, n, g, local, shapes, peak):
     """N=1 side measurements: the inner step (ours vs torch foreach) and the reference's outer step on this GPU."""
     extras = {}
-    # (3) inner step: nd_sumsq + nd_adamw(+zero-grad) over the same flat space, 32 B/elem
-    grad = torch.empty(n, device=dev).normal_(0, 1e-3, generator=g)
+    # (3) inner step the way the wrapper runs it by default: gradients are separate tensors (as autograd
+    # allocates them), p / exp_avg / exp_avg_sq are views of flat buffers; nd_sumsq_mt + nd_adamw_mt over a
+    # device table, no zeroing store (`.grad = None` afterwards, diloco.py:60): 32 B/elem algorithmic
+    from nanodiloco_b200.flat import FlatLayout
+    metas = [torch.empty(sh, device="meta") for sh in shapes]
+    lay = FlatLayout.plan(metas, quantum=4, align=4)
     m1, v1 = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    grads = [torch.empty(sh, device=dev).normal_(0, 1e-3, generator=g) for sh in shapes]
+    rows = list(zip(lay.views(local[:lay.total]), grads, lay.views(m1[:lay.total]), lay.views(v1[:lay.total])))
+    tab, T, chunks = _lib.make_table(rows, dev)
+    gtab, gT, gchunks = _lib.make_table([(gr,) for gr in grads], dev)
     ss, sc = torch.zeros(1, device=dev), _lib.scratch(dev)
+    L, st = _lib.load(), _lib._stream()
     Ki = 10
 
     def inner(step_no):
+        _lib.check(L.nd_sumsq_mt(gtab.data_ptr(), gT, gchunks, _lib.ND_F32, ss.data_ptr(), sc.data_ptr(), st))
+        _lib.check(L.nd_adamw_mt(tab.data_ptr(), T, chunks, _lib.ND_F32, 4e-4, 0.9, 0.999, 1e-8, 1e-2, step_no,
+                                 ss.data_ptr(), 1.0, 0, st))
+
+    def timed(fn):
+        for i in range(3):
+            fn(i + 1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        a.record()
+        for i in range(Ki):
+            fn(i + 4)
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / Ki
+
+    i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    inner_ms = timed(inner)
+    extras["inner_step"] = {"ms": inner_ms, "algorithmic_gbs": 32.0 * n / (inner_ms * 1e-3) / 1e9,
+                            "frac_of_hbm_peak": 32.0 * n / (inner_ms * 1e-3) / 1e9 / peak,
+                            "what": "nd_sumsq_mt + nd_adamw_mt over the model's %d gradient tensors with the clip "
+                                    "coefficient read on the device (diloco.py:57-60), no zeroing store: 32 B/elem "
+                                    "algorithmic" % len(shapes)}
+    del grads, rows, tab, gtab
+    # the flat-gradient-buffer mode (grad_buffer='flat'): one range, AdamW zeroes the gradients as it goes (36 B/elem)
+    grad = torch.empty(n, device=dev).normal_(0, 1e-3, generator=g)
+
+    def inner_flat(step_no):
         _lib.sumsq(grad, ss, sc)
         _lib.adamw(local, grad, m1, v1, lr=4e-4, step=step_no, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
 
-    for i in range(3):
-        inner(i + 1)
-    i0, i1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    i0.record()
-    for i in range(Ki):
-        inner(i + 4)
-    i1.record()
-    torch.cuda.synchronize()
-    inner_ms = i0.elapsed_time(i1) / Ki
-    extras["inner_step"] = {"ms": inner_ms, "algorithmic_gbs": 32.0 * n / (inner_ms * 1e-3) / 1e9,
-                            "frac_of_hbm_peak": 32.0 * n / (inner_ms * 1e-3) / 1e9 / peak,
-                            "what": "nd_sumsq + nd_adamw with fused clip and zero-grad (diloco.py:57-60), "
-                                    "32 B/elem algorithmic"}
+    extras["inner_step"]["flat_zero_grad_ms"] = timed(inner_flat)
     del grad, m1, v1
     # the same inner step the way the reference runs it on a GPU: clip_grad_norm_ + AdamW.step()
     # (torch foreach kernels) over the model's 201 separate tensors
@@ -325,13 +368,17 @@ def reference_arm(args):
     shapes = workload_shapes(args.workload)
     n_total = sum(numel(s) for s in shapes)
     steps, warmup = args.steps, max(1, args.warmup)
-    cb = run_cpu_baseline(shapes, n_total, args.gpus, steps, warmup, budget_s=args.cpu_budget_s)
+    cb = run_cpu_baseline(shapes, n_total, args.gpus, steps, warmup,
+                          max_elems=args.cpu_max_elems if args.cpu_max_elems > 0 else None)
+    cfg = workload_config(args, n_total, len(shapes), args.gpus)
+    if not cb["whole_workload"]:
+        cfg["workload"] = (f"SAMPLE of {args.workload}: first {cb['sample_elems']} of {n_total} params per worker "
+                           f"(capped by host memory or --cpu-max-elems); " + cfg["workload"])
     line = {
         "impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
         "steps": steps, "warmup": warmup, "ms_per_step": cb["value"], "higher_is_better": False,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, n_total, len(shapes), args.gpus),
-        "cpu_baseline": cb,
+        "config": cfg, "cpu_baseline": cb, "partial_workload": not cb["whole_workload"],
         "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -350,6 +397,148 @@ def workload_config(args, n_total, n_tensors, world):
         "l2": "each step streams several GB per GPU (>> 126 MB L2): inputs larger than L2, no flush needed",
         "parallelism": f"diloco-dp{workers}" + (f"x{rep}" if rep > 1 else ""),
     }
+
+
+def host_link_ceiling_ms(torch, dist, dev, nbytes: int, world: int, reps: int = 3):
+    """What the host link allows for the e2e step on this box: `nbytes` host->device and `nbytes`
+    device->host from page-locked memory, both directions at once on two streams, all ranks at once;
+    device ms per repetition, max over ranks.  No kernel, no dependency between the two copies -- the
+    e2e step cannot beat this, whatever the kernels do."""
+    elems = max(1, nbytes // 4)
+    h_in = torch.empty(elems, dtype=torch.float32, pin_memory=True)
+    h_out = torch.empty(elems, dtype=torch.float32, pin_memory=True)
+    d_in, d_out = torch.empty(elems, device=dev), torch.empty(elems, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    best = None
+    for _ in range(reps + 1):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        s1.wait_stream(torch.cuda.current_stream(dev))
+        s2.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True)
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True)
+        torch.cuda.current_stream(dev).wait_stream(s1)
+        torch.cuda.current_stream(dev).wait_stream(s2)
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        best = float(t) if best is None else min(best, float(t))       # first repetition warms the path
+    return best
+
+
+# ---------------------------------------------------------------------------------------------
+# NVLink byte counters (NVML), sampled around the timed region: the wire evidence for the fused
+# compute+exchange kernel, which ncu cannot wrap (one process per GPU)
+# ---------------------------------------------------------------------------------------------
+class NvlinkCounters:
+    # nvml.h: NVML_FI_DEV_NVLINK_THROUGHPUT_DATA_TX/RX (payload) and _RAW_TX/RX (payload + protocol), KiB,
+    # scope UINT_MAX = sum over the device's links
+    FIELDS = {"data_tx": 138, "data_rx": 139, "raw_tx": 140, "raw_rx": 141}
+
+    def __init__(self, index: int):
+        self.ok, self.err = False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.read()
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = repr(e)
+
+    def read(self):
+        nv = self.nv
+        vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, 0xFFFFFFFF) for fid in self.FIELDS.values()])
+        out = {}
+        for name, v in zip(self.FIELDS, vals):
+            if v.nvmlReturn != 0:
+                raise RuntimeError(f"NVML field {name}: return code {v.nvmlReturn}")
+            out[name] = int(v.value.ullVal) * 1024          # KiB -> bytes
+        return out
+
+
+def parity_check(torch, dist, O, *, mode, world, rank, workers, replicas, dev, step_fn, local, master, mom,
+                 idx, master_pos, mom_pos, bf16, elems):
+    """ONE extra outer step from saved inputs, outside the timed region, checked against the CPU oracle:
+    every rank compares `elems` elements of its own shard (new master, momentum and working copy) with
+    oracle.outer_step run on the inputs gathered from all workers, and all ranks' whole working copies
+    are compared with each other through a 64-bit checksum.  Bit-exact where the summation order is ours
+    (one GPU, peer-memory sync); rtol 1e-6 + atol 1e-6*max|x| where NCCL or the switch fixes the order."""
+    import numpy as np
+    exact = mode in ("none", "p2p") or workers <= 2
+    # --- inputs of the elements this rank checks (its own shard: it holds their master and momentum)
+    m_in = master[master_pos].float().cpu().numpy().copy()
+    b_in = mom[mom_pos].float().cpu().numpy().copy()
+    mine = local[idx].float()
+    if world > 1:
+        # worker k's copy of rank q's elements travels to rank q (first replica of each worker sends)
+        counts = torch.tensor([idx.numel()], device=dev)
+        all_idx = [torch.empty_like(idx) for _ in range(world)]
+        dist.all_gather(all_idx, idx)
+        locs = None
+        for q in range(world):
+            piece = local[all_idx[q]].float()
+            got = [torch.empty_like(piece) for _ in range(world)] if rank == q else None
+            dist.gather(piece, got, dst=q)
+            if rank == q:
+                locs = [got[k * replicas].cpu().numpy() for k in range(workers)]
+        del counts
+    else:
+        locs = [mine.cpu().numpy()]
+    # --- the step under test
+    step_fn()
+    torch.cuda.synchronize()
+    got_m = master[master_pos].float().cpu().numpy()
+    got_b = mom[mom_pos].float().cpu().numpy()
+    got_l = local[idx].float().cpu().numpy()
+    # --- oracle
+    om, ob = m_in.copy(), b_in.copy()
+    O.outer_step(om, [np.ascontiguousarray(l) for l in locs], ob, lr=OUTER_LR, momentum=OUTER_MU, first_step=False)
+    want_l = om
+    if bf16:
+        want_l = torch.from_numpy(om).to(torch.bfloat16).float().numpy()
+
+    def ulps(a, b):
+        ai = a.view(np.int32).astype(np.int64)
+        bi = b.view(np.int32).astype(np.int64)
+        ai = np.where(ai < 0, np.int64(-(2 ** 31)) - ai, ai)
+        bi = np.where(bi < 0, np.int64(-(2 ** 31)) - bi, bi)
+        return int(np.abs(ai - bi).max()) if a.size else 0
+
+    max_ulp = max(ulps(got_m, om), ulps(got_b, ob))
+    if exact:
+        ok = np.array_equal(got_m, om) and np.array_equal(got_b, ob) and np.array_equal(got_l, want_l)
+    else:
+        ok = all(np.allclose(g, w, rtol=1e-6, atol=1e-6 * float(np.abs(w).max()))
+                 for g, w in ((got_m, om), (got_b, ob)))
+        ok = ok and np.array_equal(got_l, torch.from_numpy(got_m).to(local.dtype).float().numpy())
+    # --- every rank's whole working copy is the same bits
+    words = local.view(torch.int16 if bf16 else torch.int32)
+    csum = words.sum(dtype=torch.int64).reshape(1)
+    identical = True
+    if world > 1:
+        lo_, hi_ = csum.clone(), csum.clone()
+        dist.all_reduce(lo_, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+        identical = bool(int(lo_) == int(hi_))
+        flag = torch.tensor([1 if ok else 0, max_ulp], device=dev, dtype=torch.int64)
+        dist.all_reduce(flag[0:1], op=dist.ReduceOp.MIN)
+        dist.all_reduce(flag[1:2], op=dist.ReduceOp.MAX)
+        ok, max_ulp = bool(int(flag[0])), int(flag[1])
+    return {"mode": mode, "elems": int(elems) * world, "elems_per_rank": int(elems), "ranks_checked": world,
+            "max_ulp": max_ulp, "ok": bool(ok and identical), "oracle_match": bool(ok),
+            "cross_rank_identical": identical, "checksum": int(csum),
+            "criterion": ("bit-exact (master, momentum, working copy) vs oracle/nd_oracle.c outer_step" if exact else
+                          "rtol 1e-6 + atol 1e-6*max|x| vs oracle/nd_oracle.c outer_step (summation order fixed by "
+                          "NCCL / the switch); working copy == cast(master) bit-exact"),
+            "what": "one extra outer step after the timed region; inputs gathered from every worker"}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -392,11 +581,13 @@ def native_arm(args):
     master = torch.empty(n, device=dev).normal_(0, 0.02, generator=g)      # same on every rank (seed 0)
     gl = torch.Generator(device=dev).manual_seed(100 + rank)
     hyper = dict(lr=OUTER_LR, momentum=OUTER_MU, dampening=0.0, weight_decay=0.0, nesterov=True)
-    ctx = pctx = None
+    ctx = pctx = nctx = None
+    pctx_exchange = None
     if mode == "p2p":
         # one fused kernel per GPU over NVLink peer memory; master and momentum sharded 1/W
         pctx = PeerContext(world, rank, n, elem_bytes=2 if bf16 else 4, group=None, device=dev,
-                           replicas=args.replicas)
+                           replicas=args.replicas, exchange=args.p2p_exchange)
+        pctx_exchange = pctx.exchange
         local = pctx.local(wdtype)[:n]
         # replicas of one worker hold identical parameters: seed the drift per worker, not per rank
         gl = torch.Generator(device=dev).manual_seed(100 + rank // max(1, args.replicas))
@@ -449,7 +640,9 @@ def native_arm(args):
 
     # ---- timed region: exactly K steps ---------------------------------------------------------
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    nvl = NvlinkCounters(local_rank) if world > 1 else None
     barrier()
+    nvl0 = nvl.read() if nvl is not None and nvl.ok else None
     if sampler:
         sampler.start()
     t0.record()
@@ -459,6 +652,7 @@ def native_arm(args):
     barrier()
     if sampler:
         sampler.stop()
+    nvl1 = nvl.read() if nvl0 is not None else None
     ms_total = torch.tensor([t0.elapsed_time(t1)], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms_total, op=dist.ReduceOp.MAX)
@@ -510,7 +704,13 @@ def native_arm(args):
     # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
     hbm_bytes = ((16.0 + 2 * lb) if world == 1 else (2 * lb + 16.0 / world if mode == "p2p" else 12.0 + 24.0 / world)) * n
     # reduce-scatter + all-gather bytes of the working copy, per direction per GPU (the roofline)
+    # Worst direction of the worst rank.  One rank per worker: every rank sends (W-1)/W of the copy as read
+    # responses and (W-1)/W as writes, and receives the same.  Workers of R replicas (configs[4]): only each
+    # worker's first replica is read, so ITS transmit side still carries (W-1) shards of read responses plus
+    # (W-1) shards of writes -- the same 2(W-1)/W -- while its receive side carries (W/R-1) + (W-1) shards and
+    # the other replicas less; the bound is unchanged, the mean load is lower.
     nvl_bytes = 0.0 if world == 1 else 2 * lb * (world - 1) / world * n
+    nvl_bytes_rx_first_replica = 0.0 if world == 1 else lb * ((workers - 1) + (world - 1)) / world * n
     step_roof = {"hbm_algorithmic_gbs": hbm_bytes / (ms * 1e-3) / 1e9,
                  "nvlink_algorithmic_gbs_per_dir": nvl_bytes / (ms * 1e-3) / 1e9,
                  "t_hbm_ms": hbm_bytes / (peak * 1e9) * 1e3, "t_nvlink_ms_at_900": nvl_bytes / 900e9 * 1e3}
@@ -519,6 +719,10 @@ def native_arm(args):
     step_roof["t_nvlink_ms_at_770_measured_peer_copy"] = nvl_bytes / 770e9 * 1e3
     step_roof["frac_of_bound_at_770"] = max(step_roof["t_hbm_ms"], nvl_bytes / 770e9 * 1e3) / ms
     step_roof["sync"] = mode
+    if args.replicas > 1:
+        step_roof["nvlink_bytes_per_dir"] = {"tx_first_replica": nvl_bytes, "rx_first_replica": nvl_bytes_rx_first_replica,
+                                             "tx_other_replicas": lb * (world - 1) / world * n,
+                                             "rx_other_replicas": lb * (workers + world - 1) / world * n}
     if world > 1 and mode in ("p2p", "nvls", "hybrid"):
         # A fused compute+exchange step is bounded by the slower of its HBM time and its NVLink time; at
         # W >= 2 that is NVLink.  Denominator: the measured peer-copy bandwidth of this pool, 770 GB/s per
@@ -530,6 +734,63 @@ def native_arm(args):
                     "algorithmic_bytes_per_launch": nvl_bytes, "kernel_ms": ms,
                     "hbm": {"achieved": achieved, "peak": peak, "frac": achieved / peak, "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": kern_bytes}}
+
+    # ---- NVLink bytes per step from the NVML counters (per direction, worst rank) -----------------
+    nvlink_measured = None
+    if world > 1:
+        if nvl1 is not None:
+            d = torch.tensor([(nvl1[k] - nvl0[k]) / K for k in ("data_tx", "data_rx", "raw_tx", "raw_rx")],
+                             device=dev, dtype=torch.float64)
+            dmax = d.clone()
+            dist.all_reduce(dmax, op=dist.ReduceOp.MAX)
+            nvlink_measured = {"data_tx_bytes_per_step": float(dmax[0]), "data_rx_bytes_per_step": float(dmax[1]),
+                               "raw_tx_bytes_per_step": float(dmax[2]), "raw_rx_bytes_per_step": float(dmax[3]),
+                               "algorithmic_bytes_per_dir_per_step": nvl_bytes,
+                               "source": "NVML NVLINK_THROUGHPUT_DATA/RAW_TX/RX counters (sum over links) read "
+                                         "before and after the timed region, max over ranks"}
+            per_dir = max(float(dmax[0]), float(dmax[1]))
+            if per_dir > 0:
+                nvlink_measured["traffic_over_algorithmic"] = per_dir / nvl_bytes if nvl_bytes else None
+                if roofline.get("bound") == "nvlink":
+                    roofline["traffic"] = per_dir
+                    roofline["traffic_source"] = "NVML NVLink data counters, per direction, worst rank, this run"
+        else:
+            nvlink_measured = {"error": nvl.err if nvl is not None else "unavailable"}
+
+    # ---- parity: one extra outer step from saved inputs against the CPU oracle (outside the timed region)
+    parity = None
+    if not args.no_parity:
+        try:
+            from oracle import oracle as O               # the checker; never on the timed path
+            from nanodiloco_b200.sync import shard_index_map, hybrid_index_map
+            local.add_(torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl).to(wdtype))   # workers drift apart
+            S = int(args.parity_elems)
+            if mode == "none":
+                S = min(S, n)
+                a0 = (n - S) // 2 // 4 * 4
+                idx = torch.arange(a0, a0 + S, device=dev)
+                mpos = bpos = idx
+            elif mode == "p2p":
+                lo, hi = pctx.shard_range()
+                S = min(S, hi - lo)
+                a0 = (hi - lo - S) // 2 // 4 * 4
+                bpos = mpos = torch.arange(a0, a0 + S, device=dev)
+                idx = mpos + lo
+            else:
+                full = (shard_index_map(n, world, rank, ctx.bucket) if mode == "nccl"
+                        else hybrid_index_map(n, nctx.n_nvls, world, rank, nctx.bucket))
+                S = min(S, full.numel())
+                h = S // 2
+                bpos = torch.cat([torch.arange(0, h), torch.arange(full.numel() - (S - h), full.numel())]).to(dev)
+                idx = full.to(dev)[bpos]
+                mpos = idx                                   # these modes keep a full master replica
+            parity = parity_check(torch, dist, O, mode=mode, world=world, rank=rank, workers=workers,
+                                  replicas=max(1, args.replicas), dev=dev, step_fn=step, local=local, master=master,
+                                  mom=mom, idx=idx, master_pos=mpos, mom_pos=bpos, bf16=bf16, elems=S)
+            del idx, mpos, bpos
+            torch.cuda.empty_cache()
+        except Exception as e:  # noqa: BLE001  (reported, never hidden: ok stays false)
+            parity = {"mode": mode, "ok": False, "error": repr(e)}
 
     # ---- e2e: last-sync copy in pinned HOST memory, H2D + D2H inside the timed region ------------
     e2e = None
@@ -559,10 +820,21 @@ def native_arm(args):
                        "streamed H2D -> fused kernel -> D2H in %.0f MiB chunks over 3 streams" % args.offload_chunk_mb}
         octx.close()
         del master_host, staging
+        try:
+            ceil = host_link_ceiling_ms(torch, dist, dev, 4 * n, 1)
+            e2e["host_link_ceiling_ms"] = ceil
+            e2e["frac_of_host_link_ceiling"] = ceil / e2e["value"]
+            e2e["host_link_gbs_per_dir"] = 4 * n / (ceil * 1e-3) / 1e9
+            e2e["ceiling_what"] = ("bare pinned cudaMemcpyAsync of the same bytes, H2D and D2H at once on two streams, "
+                                   "no kernel: the PCIe/host-memory bound of this box for this step")
+        except Exception as e:  # noqa: BLE001
+            e2e["host_link_ceiling_error"] = repr(e)
     elif mode == "p2p" and not args.no_e2e:
         Ke = max(2, min(K, args.e2e_steps))
         shard = master.numel()
-        chunk = max(4, min(int(args.offload_chunk_mb * (1 << 20)) // 4, shard) // 4 * 4)
+        # a 1/W shard is only a few hundred MB: smaller chunks so that it still pipelines over the 3 slots
+        chunk_mb = min(args.offload_chunk_mb, 16.0)
+        chunk = max(4, min(int(chunk_mb * (1 << 20)) // 4, shard) // 8 * 8)
         master_host = torch.empty(shard, dtype=torch.float32, pin_memory=True)
         master_host.copy_(master)
         staging = torch.empty(3 * chunk, device=dev)
@@ -587,6 +859,15 @@ def native_arm(args):
                        "reference keeps the last-sync copy on the host), streamed H2D -> fused peer kernel -> D2H in "
                        "%.0f MiB chunks over 3 streams; bytes are the whole job's (all ranks)" % (chunk * 4 / 2**20)}
         del master_host, staging
+        try:
+            ceil = host_link_ceiling_ms(torch, dist, dev, 4 * shard, world)
+            e2e["host_link_ceiling_ms"] = ceil
+            e2e["frac_of_host_link_ceiling"] = ceil / e2e["value"]
+            e2e["host_link_gbs_per_dir_per_rank"] = 4 * shard / (ceil * 1e-3) / 1e9
+            e2e["ceiling_what"] = ("bare pinned cudaMemcpyAsync of each rank's shard bytes, H2D and D2H at once on two "
+                                   "streams, all ranks at once, no kernel: the PCIe/host-memory bound of this box")
+        except Exception as e:  # noqa: BLE001
+            e2e["host_link_ceiling_error"] = repr(e)
     if sampler:
         sampler.close()
 
@@ -623,7 +904,8 @@ def native_arm(args):
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
-            cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 3, 1, budget_s=args.cpu_budget_s)
+            cpu_baseline = run_cpu_baseline(shapes, n_real, 1, 5, 1,
+                                            max_elems=args.cpu_max_elems if args.cpu_max_elems > 0 else None)
         except Exception as e:  # noqa: BLE001
             cpu_baseline = {"error": repr(e)}
 
@@ -642,6 +924,8 @@ def native_arm(args):
             "dtype": "f32" if not bf16 else "f32 master/momentum, bf16 working copy", "data": "synthetic",
             "config": workload_config(args, n_real, len(shapes), world),
             "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
+            "parity_check": parity, "nvlink_measured": nvlink_measured,
+            "p2p_exchange": pctx_exchange,
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
             "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
@@ -677,12 +961,18 @@ def main():
                     help="N>1: fused peer-memory kernel (default) or bucketed NCCL reduce-scatter/all-gather")
     ap.add_argument("--offload-chunk-mb", type=float, default=64.0)
     ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--cpu-budget-s", type=float, default=20.0)
+    ap.add_argument("--cpu-max-elems", type=int, default=0,
+                    help="cap the CPU reference at a prefix of the tensor list with this many params (0 = whole model "
+                         "when host memory allows); a capped run says so in its line and is never scaled up")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="N>1 tuning runs: skip the host-resident-master measurement")
     ap.add_argument("--no-tokens", action="store_true", help="skip the tokens/s training-loop measurement")
     ap.add_argument("--tokens-inner-steps", type=int, default=10)
     ap.add_argument("--no-extras", action="store_true", help="skip the inner-step and reference-GPU-path timings")
+    ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of one extra step")
+    ap.add_argument("--parity-elems", type=int, default=1 << 24, help="elements per rank the parity check compares")
+    ap.add_argument("--p2p-exchange", choices=["auto", "pull", "push"], default="auto",
+                    help="--sync p2p: how the worker copies reach the shard owner (nd_peer_set_mode)")
     args = ap.parse_args()
     if args.impl == "reference":
         return reference_arm(args)

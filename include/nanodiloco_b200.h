@@ -163,8 +163,10 @@ int nd_sumsq(const void* g, int dtype, int64_t n, float* out, void* scratch,
 #define ND_SUMSQ_STATIC_MAX_ELEMS (1LL << 31)
 int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t stream);
 
-/* Multi-tensor form: ptr[0]=grad. */
-int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+/* Multi-tensor form: ptr[0]=grad (`dtype` of the gradients: ND_F32 or ND_BF16).  One launch over the
+ * gradient tensors autograd allocated -- what clip_grad_norm_ (diloco.py:57) does in ~3 foreach
+ * launches over per-tensor norms. */
+int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int dtype,
                 float* out, void* scratch, nd_stream_t stream);
 
 /* Fused clip + AdamW (diloco.py:57-58; torch:nn/utils/clip_grad.py:165-174,
@@ -194,8 +196,14 @@ int nd_adamw_bf16(void* p_bf16, void* g_bf16, float* m, float* v, int64_t n,
                   int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
                   nd_stream_t stream);
 
-/* Multi-tensor form: ptr[0]=p, ptr[1]=g, ptr[2]=m, ptr[3]=v. */
-int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks,
+/* Multi-tensor form: ptr[0]=p, ptr[1]=g, ptr[2]=m, ptr[3]=v; `dtype` is the type of p and g (ND_F32,
+ * or ND_BF16 with fp32 moments as in nd_adamw_bf16).  This is the form the drop-in wrapper uses by
+ * default: the gradients stay the tensors autograd allocated, so the step can end with
+ * `.grad = None` exactly like diloco.py:60 (`zero_grad()`, set_to_none) and pays no zeroing store
+ * (zero_grad = 0: 28 B/element).  TMA-staged like nd_adamw; a row whose pointers are not 16-byte
+ * aligned is processed with plain loads and stores.  The table is read when the kernel RUNS: keep it
+ * (and the tensors it names) alive and unchanged until then. */
+int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int dtype,
                 double lr, double beta1, double beta2, double eps, double weight_decay,
                 int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
                 nd_stream_t stream);
@@ -355,6 +363,24 @@ int nd_outer_sync_hybrid(nd_peer_ctx* ctx, float* local, float* pg, float* mc_lo
                          int64_t bucket_elems, float lr, float mu, float dampening, float wd,
                          int nesterov, int first_step, nd_stream_t stream);
 int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
+
+/* How the W worker copies reach the owner of a shard in nd_outer_sync_p2p (replaces the collective
+ * of diloco.py:49 either way; same result bit for bit, same 8(W-1)/W wire bytes per element):
+ *   ND_PEER_PULL  the owner's fused kernel reads the remote copies (bulk loads over NVLink).
+ *   ND_PEER_PUSH  every worker first writes its slice into the owner's staging slots (a copy kernel of
+ *                 bulk stores), a flag barrier, then the owner's fused kernel reads local HBM only and
+ *                 writes the new parameters out: the links carry write traffic only.
+ * Push needs a staging area INSIDE every rank's peer buffer (the same offset on every rank), of at
+ * least (world / replicas) * (n_padded / world) * element bytes: nd_peer_set_staging, then
+ * nd_peer_set_mode.  The working copy then ends where the staging area starts. */
+enum { ND_PEER_PULL = 0, ND_PEER_PUSH = 1 };
+int nd_peer_set_staging(nd_peer_ctx* ctx, size_t byte_offset, size_t bytes);
+int nd_peer_set_mode(nd_peer_ctx* ctx, int mode);
+
+/* nd_peer_last_ms plus the part of it spent in the first flag barrier of nd_outer_sync_p2p, i.e.
+ * waiting for the slowest worker to arrive (the skew the reference's blocking all_reduce, diloco.py:49,
+ * hides inside the collective).  work = total - wait. */
+int nd_peer_last_ms2(nd_peer_ctx* ctx, float* total_ms_out, float* wait_ms_out);
 
 #ifdef __cplusplus
 }

@@ -16,6 +16,7 @@ ND_CHUNK = 16384
 ND_MAX_WORKERS = 16
 ND_UNIQUE_ID_BYTES = 128
 ND_IPC_HANDLE_BYTES = 64
+ND_PEER_PULL, ND_PEER_PUSH = 0, 1
 
 _c_i64 = ctypes.c_int64
 _c_f = ctypes.c_float
@@ -39,12 +40,12 @@ SIGNATURES = {
     "nd_outer_fused_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_f, _c_f, _c_f, _c_f, _c_i, _c_i, _c_p]),
     "nd_sumsq": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
     "nd_sumsq_static": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p]),
-    "nd_sumsq_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
+    "nd_sumsq_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_p, _c_p, _c_p]),
     "nd_adamw": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
                         _c_i, _c_p]),
     "nd_adamw_bf16": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
                              _c_i, _c_p]),
-    "nd_adamw_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f, _c_i, _c_p]),
+    "nd_adamw_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f, _c_i, _c_p]),
     "nd_nccl_unique_id": (_c_i, [ctypes.c_char_p]),
     "nd_sync_ctx_create": (_c_i, [ctypes.c_char_p, _c_i, _c_i, _c_i64, _c_i, ctypes.POINTER(_c_p)]),
     "nd_sync_ctx_destroy": (_c_i, [_c_p]),
@@ -72,6 +73,9 @@ SIGNATURES = {
     "nd_outer_sync_hybrid": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_p, _c_i64, _c_i64, _c_i64, _c_f, _c_f, _c_f,
                                     _c_f, _c_i, _c_i, _c_p]),
     "nd_peer_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
+    "nd_peer_set_staging": (_c_i, [_c_p, ctypes.c_size_t, ctypes.c_size_t]),
+    "nd_peer_set_mode": (_c_i, [_c_p, _c_i]),
+    "nd_peer_last_ms2": (_c_i, [_c_p, ctypes.POINTER(_c_f), ctypes.POINTER(_c_f)]),
 }
 
 _lib: Optional[ctypes.CDLL] = None

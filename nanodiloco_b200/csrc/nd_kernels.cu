@@ -437,6 +437,13 @@ struct AdamTileOpT {
     AdamWOpT<BF16> o;
     __device__ __forceinline__ void prologue() { o.prologue(); }
     __device__ __forceinline__ float acc() const { return 0.0f; }
+    // table-driven launches: bytes per element of table column k (p, g, exp_avg, exp_avg_sq)
+    static __device__ __forceinline__ int esz(int k) { return k < 2 ? kEsz : 4; }
+    __device__ __forceinline__ void rebase(const tma::TileDesc& td) {
+        using PG = typename AdamWOpT<BF16>::PG;
+        o.p = static_cast<PG*>(td.ptr[0]); o.g = static_cast<PG*>(td.ptr[1]);
+        o.m = static_cast<float*>(td.ptr[2]); o.v = static_cast<float*>(td.ptr[3]);
+    }
     __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * (8u + 2u * kEsz); }
     template <int TILE>
     __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
@@ -614,6 +621,30 @@ static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_ou
     return check_launch("tile_kernel");
 }
 
+// Table-driven TMA-staged launch (tma::tile_table_kernel): one tile = TILE elements of one tensor.
+template <int TILE, int STAGES, int THREADS, int MINB, class TileOp>
+static int launch_tile_table(const TileOp& op, const nd_tensor_desc* tab, int T, int64_t chunks, void* scratch,
+                             float* sum_out, cudaStream_t s) {
+    if ((T == 0 || chunks == 0) && !TileOp::kHasSum) return ND_OK;
+    auto kernel = tma::tile_table_kernel<TILE, STAGES, THREADS, MINB, TileOp>;
+    constexpr size_t smem = (size_t)STAGES * TileOp::kBufs * TILE * sizeof(float);
+    static_assert(smem <= 200 * 1024, "stage set too large");
+    static std::atomic<bool> configured[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = 0;
+    if (!configured[dev].load(std::memory_order_acquire)) {
+        cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return set_error(ND_ECUDA, "cudaFuncSetAttribute(smem=%zu): %s", smem, cudaGetErrorString(e));
+        configured[dev].store(true, std::memory_order_release);
+    }
+    const int64_t ntiles = chunks * (ND_CHUNK / TILE);
+    const int64_t full = (int64_t)sm_count() * MINB;
+    int64_t g = ntiles < full ? (ntiles > 0 ? ntiles : 1) : full;
+    if (g > kMaxPartials) g = kMaxPartials;
+    kernel<<<(int)g, THREADS, smem, s>>>(op, tab, T, chunks, static_cast<Scratch*>(scratch), sum_out);
+    return check_launch("tile_table_kernel");
+}
+
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 static OuterHyper make_outer_hyper(float lr, float mu, float dampening, float wd, int nesterov, int first) {
@@ -718,7 +749,7 @@ using namespace nd;
 
 extern "C" {
 
-int nd_version(void) { return 100; }
+int nd_version(void) { return 200; }
 
 const char* nd_last_error(void) { return nd::last_error(); }
 
@@ -899,10 +930,16 @@ int nd_sumsq_static(const void* g, int dtype, int64_t n, float* out, nd_stream_t
     return launch_flat<U_SUMSQ, B_SUMSQ>(op, n, sc, out, s);
 }
 
-int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, float* out, void* scratch,
-                nd_stream_t stream) {
+int nd_sumsq_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int dtype, float* out,
+                void* scratch, nd_stream_t stream) {
     ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
     ND_REQUIRE((n_tensors == 0 || table_dev) && out && scratch, "null pointer");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
+    if (dtype == ND_BF16) {
+        SumsqOp<true> op{nullptr, 0.f};
+        return launch_table<U_SUMSQ, B_SUMSQ>(op, table_dev, n_tensors, total_chunks, scratch, out,
+                                              reinterpret_cast<cudaStream_t>(stream));
+    }
     SumsqOp<false> op{nullptr, 0.f};
     return launch_table<U_SUMSQ, B_SUMSQ>(op, table_dev, n_tensors, total_chunks, scratch, out,
                                           reinterpret_cast<cudaStream_t>(stream));
@@ -941,17 +978,27 @@ int nd_adamw_bf16(void* p, void* g, float* m, float* v, int64_t n, double lr, do
     return launch_flat<U_ADAM, B_ADAM>(op, n, nullptr, nullptr, reinterpret_cast<cudaStream_t>(stream));
 }
 
-int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, double lr, double beta1,
-                double beta2, double eps, double weight_decay, int64_t step, const float* sumsq_dev,
+int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_chunks, int dtype, double lr,
+                double beta1, double beta2, double eps, double weight_decay, int64_t step, const float* sumsq_dev,
                 float max_norm, int zero_grad, nd_stream_t stream) {
     ND_REQUIRE(n_tensors >= 0 && total_chunks >= 0, "negative count");
     ND_REQUIRE(n_tensors == 0 || table_dev, "null table");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
     ND_REQUIRE(step >= 1, "step must be >= 1 (1-based)");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    // TMA-staged, table-driven: rows with unaligned pointers fall back to plain accesses inside the kernel
+    if (dtype == ND_BF16) {
+        AdamWOpT<true> op;
+        op.p = op.g = nullptr; op.m = op.v = nullptr; op.sumsq = sumsq_dev; op.coef = 1.f;
+        op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+        AdamTileOpT<true> t{op};
+        return launch_tile_table<ND_TILE_ADAM>(t, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
+    }
     AdamWOp op;
     op.p = op.g = op.m = op.v = nullptr; op.sumsq = sumsq_dev; op.coef = 1.f;
     op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
-    return launch_table<U_ADAM, B_ADAM>(op, table_dev, n_tensors, total_chunks, nullptr, nullptr,
-                                        reinterpret_cast<cudaStream_t>(stream));
+    AdamTileOp t{op};
+    return launch_tile_table<ND_TILE_ADAM>(t, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
 }
 
 }  // extern "C"

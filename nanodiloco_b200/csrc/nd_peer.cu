@@ -14,12 +14,14 @@
 // enough.  Same wire bytes as reduce-scatter + all-gather: 8*(W-1)/W bytes per element per direction.
 //
 // Replaces nanodiloco/diloco/diloco.py:46-54 including the collective of :49.
+#include <atomic>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
 
 #include "nd_common.cuh"
 #include "nd_error.h"
+#include "nd_tma.cuh"
 
 namespace nd {
 
@@ -61,6 +63,66 @@ __global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int 
         }
     }
     __threadfence_system();
+}
+
+// ---- push: every worker WRITES its slice of the working copy into the owner's staging area ------
+// The pull form of the fused kernel reads W-1 remote copies; a remote read costs a request packet
+// against the flow of the data, so with reads and writes both crossing the links each direction
+// carries payload plus the other direction's requests.  In the push form nothing is ever read over
+// NVLink: rank w bulk-stores local_w[shard r] into slot [worker(w)] of rank r's staging area for every
+// owner r, and after a flag barrier rank r's fused kernel finds all W copies in its own HBM (which has
+// bandwidth to spare) and only WRITES the new parameters out.  Wire bytes are the same 8(W-1)/W per
+// element per direction; the links see pure write traffic.
+//
+// The kernel is a copy: no arithmetic, so ONE thread per CTA drives a ring of shared-memory stages
+// with bulk loads (local HBM -> shared) and bulk stores (shared -> peer HBM).  Tile t of the launch
+// goes to destination t % n_dst so that all links carry traffic at any moment.
+struct PushArgs {
+    const char* src;                    // this rank's working copy (byte 0 of shard 0)
+    char* dst[ND_MAX_WORKERS];          // per destination: its staging slot for this worker
+    int dst_shard[ND_MAX_WORKERS];      // which shard of the flat space that destination owns
+    int n_dst;
+    int64_t shard_bytes;
+};
+
+template <int TILE_BYTES, int STAGES, int STORES>
+__global__ void __launch_bounds__(32, 2) push_kernel(PushArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ uint64_t full[STAGES];
+    if (threadIdx.x != 0) return;
+    const int64_t tiles_per_dst = (a.shard_bytes + TILE_BYTES - 1) / TILE_BYTES;
+    const int64_t ntiles = tiles_per_dst * a.n_dst;
+    for (int s = 0; s < STAGES; ++s) tma::mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    auto where = [&](int64_t t, int& d, int64_t& off, uint32_t& len) {
+        d = (int)(t % a.n_dst);
+        off = (t / a.n_dst) * (int64_t)TILE_BYTES;
+        const int64_t left = a.shard_bytes - off;
+        len = (uint32_t)(left < TILE_BYTES ? left : TILE_BYTES);
+    };
+    auto load = [&](int64_t t, int s) {
+        int d; int64_t off; uint32_t len;
+        where(t, d, off, len);
+        tma::mbar_expect_tx(&full[s], len);
+        tma::bulk_load(smem_raw + (size_t)s * TILE_BYTES, a.src + (int64_t)a.dst_shard[d] * a.shard_bytes + off, len,
+                       &full[s]);
+    };
+    // CTA-local tile k is launch tile blockIdx.x + k * gridDim.x
+    const int64_t mine = ntiles > blockIdx.x ? (ntiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    for (int k = 0; k < STAGES && k < mine; ++k) load(blockIdx.x + (int64_t)k * gridDim.x, k);
+    for (int64_t k = 0; k < mine; ++k) {
+        const int s = (int)(k % STAGES);
+        tma::mbar_wait(&full[s], (uint32_t)((k / STAGES) & 1));
+        int d; int64_t off; uint32_t len;
+        where(blockIdx.x + k * gridDim.x, d, off, len);
+        tma::bulk_store(a.dst[d] + off, smem_raw + (size_t)s * TILE_BYTES, len);
+        tma::bulk_commit();
+        // at most STORES-1 stores may still be reading shared memory: the stage of tile k-(STORES-1) is free
+        asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(STORES - 1) : "memory");
+        const int64_t j = k - (STORES - 1);
+        if (j >= 0 && j + STAGES < mine) load(blockIdx.x + (j + STAGES) * gridDim.x, (int)(j % STAGES));
+    }
+    tma::bulk_wait_all();   // every byte has left for its destination before the kernel ends
 }
 
 // ---- NVLS: the cross-worker sum is taken INSIDE the NVSwitch ---------------------------------
@@ -125,9 +187,13 @@ struct nd_peer_ctx {
     static constexpr int kChannels = 4;
     uint32_t epoch[kChannels] = {0, 0, 0, 0};
     int replicas = 1;                 // consecutive ranks that hold identical copies of one worker
+    size_t staging_off = 0, staging_bytes = 0;   // push mode: where in every rank's buffer the staging slots start
+    int mode = 0;                     // 0 = pull (remote reads + remote writes), 1 = push (remote writes only)
+    cudaEvent_t ta = nullptr, tb = nullptr;      // around the flag barrier that absorbs the skew between workers
     bool owns_mappings = true;        // false: the peer addresses were mapped by the caller (symmetric memory)
     cudaEvent_t t0 = nullptr, t1 = nullptr;
     bool timed = false;
+    bool split = false;               // the last sync recorded ta/tb (nd_outer_sync_p2p does)
     // side streams for the host-resident-master variant (created on first use)
     static constexpr int kStreams = 4;
     cudaStream_t streams[kStreams] = {nullptr, nullptr, nullptr, nullptr};
@@ -158,6 +224,8 @@ static int peer_ctx_finish(nd_peer_ctx* c) {
     c->timeout_ns = peer_timeout_ns();
     ND_CUDA(cudaEventCreate(&c->t0));
     ND_CUDA(cudaEventCreate(&c->t1));
+    ND_CUDA(cudaEventCreate(&c->ta));
+    ND_CUDA(cudaEventCreate(&c->tb));
     return ND_OK;
 }
 
@@ -265,6 +333,8 @@ int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     if (c->diag_host) cudaFreeHost(c->diag_host);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
+    if (c->ta) cudaEventDestroy(c->ta);
+    if (c->tb) cudaEventDestroy(c->tb);
     delete c;
     return ND_OK;
 }
@@ -304,31 +374,110 @@ int nd_peer_barrier(nd_peer_ctx* c, nd_stream_t stream) {
     return peer_barrier_ch(c, 0, reinterpret_cast<cudaStream_t>(stream));
 }
 
+int nd_peer_set_staging(nd_peer_ctx* c, size_t byte_offset, size_t bytes) {
+    if (!c) return set_error(ND_ESTATE, "nd_peer_set_staging: null context");
+    if (byte_offset % 256 != 0 || byte_offset + bytes > c->bytes)
+        return set_error(ND_EINVAL, "nd_peer_set_staging: the staging area must start on a 256-byte boundary inside "
+                                    "the peer buffer");
+    c->staging_off = byte_offset;
+    c->staging_bytes = bytes;
+    return ND_OK;
+}
+
+int nd_peer_set_mode(nd_peer_ctx* c, int mode) {
+    if (!c) return set_error(ND_ESTATE, "nd_peer_set_mode: null context");
+    if (mode != ND_PEER_PULL && mode != ND_PEER_PUSH) return set_error(ND_EINVAL, "nd_peer_set_mode: unknown mode");
+    if (mode == ND_PEER_PUSH && c->staging_bytes == 0)
+        return set_error(ND_ESTATE, "nd_peer_set_mode: push needs a staging area (nd_peer_set_staging)");
+    c->mode = mode;
+    return ND_OK;
+}
+
+// ND_PUSH_VARIANT (tuning knob): stage shape of the push kernel
+static int push_launch(const PushArgs& a, cudaStream_t stream) {
+    static int v = -1;
+    if (v < 0) { const char* e = getenv("ND_PUSH_VARIANT"); v = e ? atoi(e) : 0; }
+    int sms = 148, dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+#define ND_PUSH(TB, ST, SO, CTAS)                                                                            \
+    do {                                                                                                     \
+        auto k = push_kernel<TB, ST, SO>;                                                                    \
+        static std::atomic<bool> configured[64];                                                             \
+        const int d = (dev >= 0 && dev < 64) ? dev : 0;                                                      \
+        if (!configured[d].load(std::memory_order_acquire)) {                                                \
+            ND_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (TB) * (ST)));       \
+            configured[d].store(true, std::memory_order_release);                                            \
+        }                                                                                                    \
+        k<<<sms * (CTAS), 32, (TB) * (ST), stream>>>(a);                                                     \
+    } while (0)
+    switch (v) {
+        case 1: ND_PUSH(32768, 6, 3, 1); break;
+        case 2: ND_PUSH(8192, 8, 4, 2); break;
+        case 3: ND_PUSH(16384, 4, 2, 3); break;
+        default: ND_PUSH(16384, 6, 3, 2); break;
+    }
+#undef ND_PUSH
+    return check_launch("push_kernel");
+}
+
 int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int local_dtype, int64_t n_padded,
                       float lr, float mu, float dampening, float wd, int nesterov, int first_step,
                       float* sumsq_out, void* scratch, nd_stream_t stream_) {
     if (!c) return set_error(ND_ESTATE, "nd_outer_sync_p2p: null context");
+    if (int rc = peer_diag(c, "nd_outer_sync_p2p")) return rc;
     const int W = c->world;
     if (local_dtype != ND_F32 && local_dtype != ND_BF16) return set_error(ND_EINVAL, "nd_outer_sync_p2p: unknown dtype");
     const int gran = local_dtype == ND_BF16 ? 8 : 4;
     if (n_padded < 0 || n_padded % ((int64_t)gran * W) != 0)
         return set_error(ND_EINVAL, "nd_outer_sync_p2p: n_padded must be a multiple of %d*world", gran);
     const size_t esz = local_dtype == ND_BF16 ? 2 : 4;
-    if ((size_t)n_padded * esz > c->bytes) return set_error(ND_EINVAL, "nd_outer_sync_p2p: n_padded exceeds the peer buffers");
+    const bool push = c->mode == ND_PEER_PUSH && W > 1;
+    const size_t local_limit = c->staging_bytes ? c->staging_off : c->bytes;
+    if ((size_t)n_padded * esz > local_limit) return set_error(ND_EINVAL, "nd_outer_sync_p2p: n_padded exceeds the peer buffers");
     if (n_padded && (!master_shard || !mom_shard)) return set_error(ND_EINVAL, "nd_outer_sync_p2p: null pointer");
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const int64_t shard = n_padded / W;
+    const size_t shard_bytes = (size_t)shard * esz;
+    const int workers = W / c->replicas;
+    if (push && (size_t)workers * shard_bytes > c->staging_bytes)
+        return set_error(ND_EINVAL, "nd_outer_sync_p2p: the staging area holds fewer than workers*shard bytes");
     ND_CUDA(cudaEventRecord(c->t0, stream));
     int rc;
-    if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every worker's inner steps are done
     void *reads[ND_MAX_WORKERS], *writes[ND_MAX_WORKERS];
-    const int workers = fill_rw(c, (size_t)c->rank * shard * esz, reads, writes);
+    fill_rw(c, (size_t)c->rank * shard_bytes, reads, writes);
+    if (push) {
+        // phase A: the first replica of every worker writes its copy of shard r into slot [worker] of rank r
+        if (c->rank % c->replicas == 0 && shard_bytes > 0) {
+            PushArgs a;
+            a.src = static_cast<const char*>(c->base[c->rank]);
+            a.shard_bytes = (int64_t)shard_bytes;
+            a.n_dst = 0;
+            const int me = c->rank / c->replicas;
+            for (int r = 0; r < W; ++r) {
+                if (r == c->rank) continue;      // our own shard is read in place
+                a.dst[a.n_dst] = static_cast<char*>(c->base[r]) + c->staging_off + (size_t)me * shard_bytes;
+                a.dst_shard[a.n_dst] = r;
+                ++a.n_dst;
+            }
+            if ((rc = push_launch(a, stream))) return rc;
+        }
+        // every worker's copy of OUR shard now sits in our own staging slots (after the barrier below)
+        for (int k = 0; k < workers; ++k)
+            if (k * c->replicas != c->rank)
+                reads[k] = static_cast<char*>(c->base[c->rank]) + c->staging_off + (size_t)k * shard_bytes;
+    }
+    ND_CUDA(cudaEventRecord(c->ta, stream));
+    // pull: every worker's inner steps are done.  push: every worker's slices have landed here (which
+    // also means its inner steps are done and it has finished reading its own copy)
+    if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
+    ND_CUDA(cudaEventRecord(c->tb, stream));
     rc = nd_outer_fused_rw(master_shard, mom_shard, reads, workers, writes, W, local_dtype, shard, lr, mu, dampening,
                            wd, nesterov, first_step, sumsq_out, scratch, stream_);
     if (rc) return rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every shard of our copy has been written
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
+    c->split = true;
     return ND_OK;
 }
 
@@ -388,6 +537,7 @@ int nd_outer_sync_p2p_offloaded(nd_peer_ctx* c, float* master_host_shard, float*
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
+    c->split = false;
     return ND_OK;
 }
 
@@ -507,6 +657,7 @@ int nd_outer_sync_hybrid(nd_peer_ctx* c, float* local, float* pg, float* mc_loca
     }
     ND_CUDA(cudaEventRecord(c->t1, stream));
     c->timed = true;
+    c->split = false;
     return ND_OK;
 }
 
@@ -526,6 +677,15 @@ int nd_peer_last_ms(nd_peer_ctx* c, float* ms_out) {
         return set_error(ND_ECUDA, "nd_peer_last_ms: cudaEventSynchronize failed: %s", cudaGetErrorString(es));
     }
     ND_CUDA(cudaEventElapsedTime(ms_out, c->t0, c->t1));
+    return ND_OK;
+}
+
+int nd_peer_last_ms2(nd_peer_ctx* c, float* total_ms_out, float* wait_ms_out) {
+    if (!wait_ms_out) return set_error(ND_EINVAL, "nd_peer_last_ms2: null argument");
+    if (int rc = nd_peer_last_ms(c, total_ms_out)) return rc;
+    *wait_ms_out = 0.0f;
+    // only nd_outer_sync_p2p brackets its first barrier; the other variants report wait = 0
+    if (c->split) ND_CUDA(cudaEventElapsedTime(wait_ms_out, c->ta, c->tb));
     return ND_OK;
 }
 

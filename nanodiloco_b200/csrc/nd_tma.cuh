@@ -154,5 +154,113 @@ __global__ void __launch_bounds__(THREADS, MINB) tile_kernel(TileOp op, int64_t 
     if constexpr (TileOp::kHasSum) grid_sum_to(op.acc(), sc, sum_out);
 }
 
+// ---- the same pipeline over a device TABLE of tensors -------------------------------------------
+// For callers whose arrays are not one flat range: the inner AdamW step when the gradients are the
+// tensors autograd allocated (reference semantics: `.grad` is None after every step, diloco.py:60),
+// so only p, exp_avg and exp_avg_sq live in flat buffers.  A tensor is cut into ND_CHUNK-element
+// chunks (the table's `first_chunk` numbering) and every chunk into ND_CHUNK / TILE tiles; tile
+// g = blockIdx.x + k * gridDim.x belongs to chunk g / (ND_CHUNK / TILE).  The producer thread finds
+// the row by binary search (the table is a few hundred rows, L1/L2-resident), publishes a TileDesc
+// for the consumers through shared memory (ordered by the mbarrier it then arrives on) and issues
+// the bulk loads.  Rows whose pointers are not 16-byte aligned, and the last numel % kGran
+// elements of a tensor, take plain loads and stores straight from global memory.
+struct TileDesc {
+    void* ptr[4];  // the row's pointers, advanced to this tile's first element
+    int len;       // elements of the tile (0: a chunk slot past the tensor's end)
+    int bulk;      // leading elements that travel as bulk copies (multiple of kGran; 0 when unaligned)
+};
+
+__device__ __forceinline__ void mbar_arrive(uint64_t* b) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(b)) : "memory");
+}
+
+template <int TILE, int STAGES, int THREADS, int MINB, class TileOp>
+__global__ void __launch_bounds__(THREADS, MINB)
+    tile_table_kernel(TileOp op, const nd_tensor_desc* __restrict__ tab, int T, int64_t total_chunks, Scratch* sc,
+                      float* sum_out) {
+    static_assert(ND_CHUNK % TILE == 0, "a chunk is a whole number of tiles");
+    constexpr int kTilesPerChunk = ND_CHUNK / TILE;
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float* sm = reinterpret_cast<float*>(smem_raw);
+    __shared__ uint64_t full[STAGES];
+    __shared__ TileDesc desc[STAGES];
+    constexpr int kStageFloats = TileOp::kBufs * TILE;
+    const int64_t ntiles = total_chunks * kTilesPerChunk;
+    const int tid = threadIdx.x;
+    op.prologue();
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    auto issue = [&](int64_t g, int s) {   // producer thread only
+        const int64_t chunk = g / kTilesPerChunk;
+        const int sub = (int)(g % kTilesPerChunk);
+        int lo = 0, hi = T - 1;
+        while (lo < hi) {  // last row with first_chunk <= chunk
+            const int mid = (lo + hi + 1) >> 1;
+            if (__ldg(&tab[mid].first_chunk) <= chunk) lo = mid; else hi = mid - 1;
+        }
+        const nd_tensor_desc d = tab[lo];
+        const int64_t off = (chunk - d.first_chunk) * (int64_t)ND_CHUNK + (int64_t)sub * TILE;
+        int64_t len = d.numel - off;
+        len = len < 0 ? 0 : (len > TILE ? TILE : len);
+        TileDesc td;
+        uintptr_t bits = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            td.ptr[k] = d.ptr[k] ? static_cast<char*>(d.ptr[k]) + off * TileOp::esz(k) : nullptr;
+            bits |= reinterpret_cast<uintptr_t>(td.ptr[k]);
+        }
+        td.len = (int)len;
+        td.bulk = (bits & 15) ? 0 : ((int)len & ~(TileOp::kGran - 1));
+        desc[s] = td;
+        if (td.bulk > 0) {
+            TileOp o = op;
+            o.rebase(td);
+            Stage<TILE> st{sm + (size_t)s * kStageFloats};
+            mbar_expect_tx(&full[s], o.load_bytes(td.bulk));
+            o.loads(st, 0, td.bulk, &full[s]);
+        } else {
+            mbar_arrive(&full[s]);   // nothing in flight for this tile; the arrival publishes desc[s]
+        }
+    };
+
+    if (tid == 0) {
+        for (int k = 0; k < STAGES - 1; ++k) {
+            const int64_t g = blockIdx.x + (int64_t)k * gridDim.x;
+            if (g < ntiles) issue(g, k);
+        }
+    }
+    int it = 0;
+    for (int64_t g = blockIdx.x; g < ntiles; g += gridDim.x, ++it) {
+        const int s = it % STAGES;
+        if (tid == 0) {
+            const int64_t gnext = g + (int64_t)(STAGES - 1) * gridDim.x;
+            if (gnext < ntiles) {
+                bulk_wait_read_all();  // the stores that read the stage being refilled have drained
+                issue(gnext, (it + STAGES - 1) % STAGES);
+            }
+        }
+        mbar_wait(&full[s], (it / STAGES) & 1);
+        const TileDesc td = desc[s];   // into registers: the producer rewrites desc[s] STAGES-1 tiles from now
+        TileOp o = op;
+        o.rebase(td);
+        Stage<TILE> st{sm + (size_t)s * kStageFloats};
+        if (td.bulk > 0) o.compute(st, td.bulk, tid, THREADS);
+        fence_async();
+        __syncthreads();
+        if (tid == 0 && td.bulk > 0) {
+            o.stores(st, 0, td.bulk);
+            bulk_commit();
+        }
+        for (int i = td.bulk + tid; i < td.len; i += THREADS) o.tail(i);
+        if constexpr (TileOp::kHasSum) op.add_acc(o.acc());
+    }
+    if (tid == 0) bulk_wait_all();
+    if constexpr (TileOp::kHasSum) grid_sum_to(op.acc(), sc, sum_out);
+}
+
 }  // namespace tma
 }  // namespace nd

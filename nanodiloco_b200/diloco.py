@@ -28,6 +28,7 @@ There is no CPU path: constructing this class with CPU parameters raises.
 from __future__ import annotations
 
 import math
+import os
 from typing import List, Optional
 
 import torch
@@ -35,6 +36,21 @@ import torch.distributed as dist
 
 from . import _lib
 from .flat import FlatLayout, rehome_, trainable_runs
+
+
+_NVTX = os.environ.get("ND_NVTX") == "1"
+
+
+def _nvtx_push(name: str) -> None:
+    """NVTX range around a phase of the hot path (visible in nsys / ncu --nvtx); off unless ND_NVTX=1,
+    because every push is a Python -> C call on a path that otherwise launches one or two kernels."""
+    if _NVTX:
+        torch.cuda.nvtx.range_push(name)
+
+
+def _nvtx_pop() -> None:
+    if _NVTX:
+        torch.cuda.nvtx.range_pop()
 
 
 def _cosine_schedule_with_warmup(optimizer, num_warmup_steps: int, num_training_steps: int):
@@ -76,6 +92,8 @@ class Diloco:
         sync: str = "auto",
         replicas_per_worker: int = 1,
         nvls_fraction: float = 0.75,
+        grad_buffer: str = "auto",
+        p2p_exchange: str = "auto",
     ):
         # diloco.py:17-20
         self.model = model
@@ -165,7 +183,7 @@ class Diloco:
         elif self.sync_mode == "p2p":
             from .sync import PeerContext
             self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
-                                     device=dev, replicas=self.replicas)
+                                     device=dev, replicas=self.replicas, exchange=p2p_exchange)
             self._local = self._peer.local(wdtype)[:n]
         else:
             if self.sync_mode == "nccl" and wdtype != torch.float32:
@@ -185,6 +203,10 @@ class Diloco:
         self.offload_master = offload_master
         self._first_outer = True
         self._scratch = _lib.scratch(dev)
+        # sum of squares of the averaged pseudo-gradient, one slot per outer param group (this rank's
+        # shard of it when the outer state is sharded); see last_outer_grad_norm
+        self._outer_sumsq = torch.zeros(max(1, len(outer_optimizer.param_groups)), dtype=torch.float32, device=dev)
+        self._outer_sumsq_valid = False
         if offload_master:
             if W > 1 and self._peer is None:
                 raise NotImplementedError("offload_master with several workers needs sync='p2p'")
@@ -220,15 +242,35 @@ class Diloco:
             self._pg = None
 
         # ---- inner optimizer state in flat buffers --------------------------------------------
+        # Where the gradients live:
+        #   "autograd" (default)  `.grad` is whatever autograd allocated and is None again after every
+        #       inner step, exactly like the reference's `zero_grad()` (diloco.py:60).  The fused step
+        #       walks a device table of (p, grad, exp_avg, exp_avg_sq) rows (nd_sumsq_mt / nd_adamw_mt):
+        #       no zeroing store, and the first backward of the next step writes instead of accumulating.
+        #   "flat"  `.grad` are views of one flat buffer that the AdamW kernel zeroes as it goes
+        #       (4 B/element more per step).  Needed when replicas of a worker average the gradient
+        #       buffer over NVLink (replicas_per_worker > 1), useful when the allocator must stay quiet.
+        if grad_buffer not in ("auto", "autograd", "flat"):
+            raise ValueError("grad_buffer must be 'auto', 'autograd' or 'flat'")
+        if grad_buffer == "auto":
+            grad_buffer = "flat" if self.replicas > 1 else "autograd"
+        if self.replicas > 1 and grad_buffer != "flat":
+            raise ValueError("replicas_per_worker > 1 needs grad_buffer='flat'")
+        self.grad_buffer = grad_buffer
         self._grad = None
         self._inner_step_count = 0
+        self._tables = {}          # inner-step tables: key -> (row pointers, device table, T, chunks)
+        self._table_stage = None   # page-locked staging of the table upload + the event that frees it
         if fused_inner:
-            self._grad = torch.zeros(n, dtype=wdtype, device=dev)
             self._exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
             self._exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
             self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
-            self._grad_views = self.layout.views(self._grad)
-            self._attach_grads()
+            self._m_views = self.layout.views(self._exp_avg)
+            self._v_views = self.layout.views(self._exp_avg_sq)
+            if grad_buffer == "flat":
+                self._grad = torch.zeros(n, dtype=wdtype, device=dev)
+                self._grad_views = self.layout.views(self._grad)
+                self._attach_grads()
             # same keys torch.optim.AdamW creates lazily (torch:optim/adam.py:167-190).  Every parameter
             # takes the same step every time, so all of them share ONE host step counter: a single
             # increment per inner step instead of one per tensor.
@@ -247,7 +289,11 @@ class Diloco:
         # diloco.py:23-24 declares these and never updates them; here they are real
         self._sync_time = 0.0
         self._sync_calls = 0
+        self._wait_time = 0.0
+        self._wait_calls = 0
+        self._fold_wait = False
         self._pending_events: List[tuple] = []
+        self._install_state_hooks()
 
     # ------------------------------------------------------------------------------------------
     def _group_ranges(self, optimizer):
@@ -311,11 +357,15 @@ class Diloco:
         pseudo-gradient (master - local) -> average over workers -> Nesterov SGD on the
         master copy -> copy the new parameters into every worker, with the hyper-parameters
         read from `outer_optimizer.param_groups` at call time."""
+        if getattr(self, "_closed", False):
+            raise _lib.NDError("outer_step() after close()")
         stream = torch.cuda.current_stream(self.device)
         t0 = torch.cuda.Event(enable_timing=True)
         t1 = torch.cuda.Event(enable_timing=True)
+        _nvtx_push("nd.outer_step[%s]" % self.sync_mode)
         t0.record(stream)
         first = self._first_outer
+        self._outer_sumsq_valid = False
         if self.offload_master:
             if len(self._outer_ranges) != 1:
                 raise NotImplementedError("offload_master supports a single outer param group")
@@ -345,14 +395,18 @@ class Diloco:
             self._peer.outer_sync(self._master, self._mom, dtype=self.working_dtype, lr=float(g["lr"]),
                                   momentum=float(g["momentum"]),
                                   dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
-                                  nesterov=bool(g["nesterov"]), first_step=first)
+                                  nesterov=bool(g["nesterov"]), first_step=first,
+                                  sumsq_out=self._outer_sumsq[0:1], scratch_buf=self._scratch)
+            self._outer_sumsq_valid = True
         elif self._ctx is None:
-            for g, s, e in self._outer_ranges:
+            for gi, (g, s, e) in enumerate(self._outer_ranges):
                 self._check_outer_group(g)
                 _lib.outer_fused(self._master[s:e], self._mom[s:e], [self._local[s:e]],
                                  lr=float(g["lr"]), momentum=float(g["momentum"]),
                                  dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
-                                 nesterov=bool(g["nesterov"]), first_step=first)
+                                 nesterov=bool(g["nesterov"]), first_step=first,
+                                 sumsq_out=self._outer_sumsq[gi:gi + 1], scratch_buf=self._scratch)
+            self._outer_sumsq_valid = True
         else:
             if len(self._outer_ranges) != 1:
                 raise NotImplementedError("the sharded outer sync supports a single outer param group")
@@ -363,7 +417,10 @@ class Diloco:
                                  dampening=float(g["dampening"]), weight_decay=float(g["weight_decay"]),
                                  nesterov=bool(g["nesterov"]), first_step=first)
         t1.record(stream)
+        _nvtx_pop()
         self._pending_events.append((t0, t1))
+        if self._peer is not None and not self.offload_master:
+            self._fold_wait = True               # the context's own events split the step; read them lazily
         if len(self._pending_events) > 32:      # fold finished timings in; old events completed long ago
             self.avg_sync_time
         self._first_outer = False
@@ -382,6 +439,47 @@ class Diloco:
             return
         for p, v in zip(self._params, self.layout.views(self._mom)):
             self.outer_optimizer.state[p]["momentum_buffer"] = v
+
+    def _install_state_hooks(self) -> None:
+        """Keep `outer_optimizer.state_dict()` / `.load_state_dict()` and `inner_optimizer.load_state_dict()`
+        truthful although the state lives in flat (and, across GPUs, sharded) buffers of ours:
+          * before the outer optimizer serialises itself the full momentum buffers are assembled -- with
+            sharded state that is a COLLECTIVE, so every rank must call `outer_optimizer.state_dict()`
+            together (as with any sharded optimizer);
+          * after either optimizer loads a state dict torch has replaced our views by fresh tensors: their
+            contents are copied back into the flat buffers (this rank's shard of them) and the views restored."""
+        def pre_outer(optimizer):
+            if not self._first_outer:
+                self.gather_outer_state()
+
+        def post_outer(optimizer):
+            moms = [optimizer.state.get(p, {}).get("momentum_buffer") for p in self._params]
+            if all(m is None for m in moms):
+                return
+            full = torch.zeros(self.layout.total, dtype=torch.float32, device=self.device)
+            for m, v in zip(moms, self.layout.views(full)):
+                if m is not None:
+                    v.copy_(m)
+            idx = self._shard_indices()
+            self._mom.copy_(full if idx is None else full[idx])
+            self._first_outer = False
+            self._publish_outer_state()
+
+        def post_inner(optimizer):
+            if not self.fused_inner:
+                return
+            for p, m, v in zip(self._params, self._m_views, self._v_views):
+                st = optimizer.state.get(p)
+                if not st:
+                    continue
+                m.copy_(st["exp_avg"]); v.copy_(st["exp_avg_sq"])
+                self._inner_step_count = int(st["step"])
+                st["exp_avg"], st["exp_avg_sq"], st["step"] = m, v, self._step_tensor
+            self._step_tensor.fill_(float(self._inner_step_count))
+
+        self._hooks = [self.outer_optimizer.register_state_dict_pre_hook(pre_outer),
+                       self.outer_optimizer.register_load_state_dict_post_hook(post_outer),
+                       self.inner_optimizer.register_load_state_dict_post_hook(post_inner)]
 
     def gather_outer_state(self) -> None:
         """Collective: materialise the full momentum buffers into outer_optimizer.state."""
@@ -454,42 +552,110 @@ class Diloco:
             self.scheduler.step()
             self.inner_optimizer.zero_grad()
             return
-        flat_ok = all(p.grad is not None and p.grad.data_ptr() == gv.data_ptr()
-                      for p, gv in zip(self._params, self._grad_views) if p.requires_grad)
-        if not flat_ok:
-            self._adopt_foreign_grads()
+        for g in self.inner_optimizer.param_groups:
+            if g.get("amsgrad", False) or g.get("maximize", False):
+                raise NotImplementedError("fused inner AdamW does not support amsgrad/maximize")
         self._inner_step_count += 1
+        flat = self._grad is not None and all(
+            p.grad is not None and p.grad.data_ptr() == gv.data_ptr()
+            for p, gv in zip(self._params, self._grad_views) if p.requires_grad)
+        _nvtx_push("nd.inner_step")
+        if flat:
+            self._inner_step_flat()
+        else:
+            self._inner_step_tables()
+        _nvtx_pop()
+        self._step_tensor += 1
+        # the fused kernel stood in for inner_optimizer.step(); tell the LR scheduler's order check so
+        self.inner_optimizer._opt_called = True
+        self.scheduler.step()
+
+    def _inner_step_flat(self) -> None:
+        """Gradients in the flat buffer: one sum-of-squares launch and one AdamW launch per param group;
+        the AdamW pass zeroes the gradients (diloco.py:60) and `.grad` stay views of the buffer."""
         if self._intra_group is not None:
             # intra-worker data parallelism: one all-reduce of the flat gradient buffer over NVLink
             dist.all_reduce(self._grad, op=dist.ReduceOp.AVG, group=self._intra_group)
         _lib.sumsq(self._grad, self._sumsq, self._scratch)
         for g, s, e in self._inner_ranges:
-            if g.get("amsgrad", False) or g.get("maximize", False):
-                raise NotImplementedError("fused inner AdamW does not support amsgrad/maximize")
             b1, b2 = g["betas"]
             _lib.adamw(self._local[s:e], self._grad[s:e], self._exp_avg[s:e], self._exp_avg_sq[s:e],
                        lr=float(g["lr"]), beta1=float(b1), beta2=float(b2), eps=float(g["eps"]),
                        weight_decay=float(g["weight_decay"]), step=self._inner_step_count,
                        sumsq_dev=self._sumsq, max_norm=self.max_grad_norm, zero_grad=True)
-        self._step_tensor += 1
-        # the fused kernel stood in for inner_optimizer.step(); tell the LR scheduler's order check so
-        self.inner_optimizer._opt_called = True
-        self.scheduler.step()
-        # diloco.py:60 zero_grad(): fused into the AdamW pass; .grad stays a (zeroed) view of the
-        # flat gradient buffer so the next backward accumulates straight into it.
 
-    def _adopt_foreign_grads(self) -> None:
-        """A caller (or autograd after `zero_grad(set_to_none=True)`) replaced some `.grad`:
-        fold those gradients into the flat buffer and re-attach the views."""
-        with torch.no_grad():
-            for p, gv in zip(self._params, self._grad_views):
-                if not p.requires_grad:
+    def _inner_step_tables(self) -> None:
+        """Gradients wherever autograd put them: a device table per param group names (p, grad, exp_avg,
+        exp_avg_sq) of every parameter that HAS a gradient -- a parameter whose `.grad` is None is left
+        alone entirely, weight decay included, as torch's optimizers do (torch:optim/adam.py:150-160).
+        Ends with `.grad = None` like the reference's zero_grad() (diloco.py:60)."""
+        groups = self.inner_optimizer.param_groups
+        per_group, i = [], 0
+        for g in groups:
+            rows = []
+            for p in g["params"]:
+                k = i
+                i += 1
+                gr = p.grad
+                if gr is None or not p.requires_grad:
                     continue
-                if p.grad is None:
-                    gv.zero_()
-                elif p.grad.data_ptr() != gv.data_ptr():
-                    gv.copy_(p.grad)
-        self._attach_grads()
+                if gr.dtype != self.working_dtype or gr.device != self.device or gr.is_sparse:
+                    raise _lib.NDError("gradients must be dense, on the parameters' device and of their dtype")
+                if not gr.is_contiguous():
+                    gr = gr.contiguous()
+                    p.grad = gr
+                rows.append((k, gr))
+            per_group.append(rows)
+        all_rows = [r for rows in per_group for r in rows]
+        code = _lib.ND_BF16 if self.working_dtype == torch.bfloat16 else _lib.ND_F32
+        L = _lib.load()
+        stream = _lib._stream()
+        if all_rows:
+            tab, T, chunks = self._table(("norm",), all_rows, with_state=False)
+            _lib.check(L.nd_sumsq_mt(tab.data_ptr(), T, chunks, code, self._sumsq.data_ptr(), self._scratch.data_ptr(),
+                                     stream), "nd_sumsq_mt")
+        else:
+            self._sumsq.zero_()
+        for gi, (g, rows) in enumerate(zip(groups, per_group)):
+            if not rows:
+                continue
+            tab, T, chunks = self._table(("adam", gi), rows, with_state=True)
+            b1, b2 = g["betas"]
+            _lib.check(L.nd_adamw_mt(tab.data_ptr(), T, chunks, code, float(g["lr"]), float(b1), float(b2),
+                                     float(g["eps"]), float(g["weight_decay"]), self._inner_step_count,
+                                     self._sumsq.data_ptr(), self.max_grad_norm, 0, stream), "nd_adamw_mt")
+        if self._grad is not None:          # flat mode, this step had foreign or missing gradients
+            self._grad.zero_()
+            self._attach_grads()
+        else:
+            for p in self._params:
+                p.grad = None
+
+    def _table(self, key, rows, *, with_state: bool):
+        """Device table for `rows` = [(parameter index, gradient tensor)].  Parameters and moments never
+        move, gradients come from the caching allocator and usually land where they did last step: the
+        table is uploaded again only when some address differs."""
+        ptrs = tuple(g.data_ptr() for _, g in rows) + tuple(k for k, _ in rows)
+        hit = self._tables.get(key)
+        if hit is not None and hit[0] == ptrs:
+            return hit[1], hit[2], hit[3]
+        flat, chunk = [], 0
+        pv = self.layout.views(self._local) if with_state else None
+        for k, g in rows:
+            n = g.numel()
+            if with_state:
+                flat.extend([pv[k].data_ptr(), g.data_ptr(), self._m_views[k].data_ptr(), self._v_views[k].data_ptr(),
+                             n, chunk])
+            else:
+                flat.extend([g.data_ptr(), 0, 0, 0, n, chunk])
+            chunk += (n + _lib.ND_CHUNK - 1) // _lib.ND_CHUNK
+        host = torch.tensor(flat, dtype=torch.int64)
+        # the table is read when the kernel runs, so the old one must outlive launches already queued:
+        # keep a fresh device tensor per upload (a few KB) and let the caching allocator recycle old ones
+        # in stream order
+        dev_tab = host.to(self.device, non_blocking=False)
+        self._tables[key] = (ptrs, dev_tab, len(rows), chunk)
+        return dev_tab, len(rows), chunk
 
     @property
     def last_grad_norm(self) -> torch.Tensor:
@@ -501,12 +667,67 @@ class Diloco:
     def avg_sync_time(self):
         """Mean device time of `outer_step` in seconds (diloco.py:62-64 promises this and always
         returns 0 because `_sync_time` is never updated there)."""
+        self._fold_timings()
+        return self._sync_time / self._sync_calls if self._sync_calls > 0 else 0
+
+    def _fold_timings(self) -> None:
         for t0, t1 in self._pending_events:
             t1.synchronize()
             self._sync_time += t0.elapsed_time(t1) / 1e3
             self._sync_calls += 1
         self._pending_events.clear()
-        return self._sync_time / self._sync_calls if self._sync_calls > 0 else 0
+        if getattr(self, "_fold_wait", False):
+            # the peer context brackets the flag barrier that absorbs the skew between workers; only the
+            # LAST sync's split is kept by the library, so this is a running mean over the syncs observed
+            _, wait_ms = self._peer.last_ms2()
+            self._wait_time += wait_ms / 1e3
+            self._wait_calls += 1
+            self._fold_wait = False
+
+    @property
+    def avg_sync_wait_time(self):
+        """Mean seconds per outer sync spent waiting for the slowest worker to ARRIVE (the first flag
+        barrier of the peer-memory sync) -- skew between workers, not cost of the synchronisation.
+        In a training loop `avg_sync_time` contains it; `avg_sync_time - avg_sync_wait_time` is what the
+        exchange and the update themselves take.  None where the sync has no separable wait (one GPU,
+        NCCL: the skew is absorbed inside the first collective)."""
+        if self._peer is None or self.offload_master:
+            return None
+        self._fold_timings()
+        return self._wait_time / self._wait_calls if self._wait_calls else 0.0
+
+    @property
+    def last_outer_grad_norm(self):
+        """L2 norm of the averaged pseudo-gradient of the last outer step (what the outer SGD stepped on;
+        the quantity DiLoCo runs watch for divergence), computed by the fused kernel on the way.  A device
+        tensor; with sharded outer state (several GPUs) reading it is a COLLECTIVE (one all-reduce of one
+        float).  None for the sync modes that do not produce it (nccl, nvls, hybrid, host-resident master)."""
+        if not self._outer_sumsq_valid:
+            return None
+        tot = self._outer_sumsq.sum()
+        if self._peer is not None and self.world_size > 1:
+            dist.all_reduce(tot, group=self._pg_group)
+        return tot.sqrt()
+
+    def close(self) -> None:
+        """Releases what the wrapper holds outside torch's allocator: peer-mapped buffers and IPC
+        mappings, the NCCL communicator, side streams, the optimizer hooks.  A COLLECTIVE across GPUs
+        (nobody may unmap a buffer a peer kernel could still touch).  The parameters are first moved back
+        into ordinary torch memory, so the model stays usable."""
+        if getattr(self, "_closed", False):
+            return
+        self._closed = True
+        for h in getattr(self, "_hooks", []):
+            h.remove()
+        torch.cuda.current_stream(self.device).synchronize()
+        if self._peer is not None or self._nvls is not None:
+            keep = self._local.clone()
+            rehome_(self._params, keep, self.layout)
+            self._local = keep
+        for ctx in (self._peer, self._nvls, self._ctx, getattr(self, "_off_ctx", None)):
+            if ctx is not None:
+                ctx.close()
+        self._peer = self._nvls = self._ctx = None
 
     def __call__(self, *args, **kwargs):
         return self.model(*args, **kwargs)

@@ -132,12 +132,25 @@ class PeerContext:
     """
 
     def __init__(self, world: int, rank: int, n_padded: int, *, elem_bytes: int = 4, group=None, device=None,
-                 replicas: int = 1):
+                 replicas: int = 1, exchange: str = "auto"):
+        """exchange: "pull" (the owner's kernel reads the remote copies), "push" (every worker writes its
+        slices into the owners' staging slots first; needs (world/replicas)/world of the working copy's
+        size in extra peer memory per rank) or "auto" (ND_P2P_MODE if set, else pull)."""
+        import os
         L = _lib.load()
         self.world, self.rank, self.group = world, rank, group
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.n_padded = int(n_padded)
-        self.nbytes = self.n_padded * elem_bytes
+        if exchange == "auto":
+            exchange = os.environ.get("ND_P2P_MODE", "pull")
+        if exchange not in ("pull", "push"):
+            raise ValueError("exchange must be 'pull', 'push' or 'auto'")
+        self.exchange = exchange if world > 1 else "pull"
+        local_bytes = (self.n_padded * elem_bytes + 255) // 256 * 256
+        staging_bytes = 0
+        if self.exchange == "push":
+            staging_bytes = (world // int(replicas)) * (self.n_padded // world) * elem_bytes
+        self.nbytes = local_bytes + staging_bytes
         ptr = ctypes.c_void_p()
         handle = ctypes.create_string_buffer(_lib.ND_IPC_HANDLE_BYTES)
         with torch.cuda.device(self.device):
@@ -156,17 +169,21 @@ class PeerContext:
         self.replicas = int(replicas)
         if self.replicas != 1:
             _lib.check(L.nd_peer_set_replicas(self._h, self.replicas), "nd_peer_set_replicas")
+        if staging_bytes:
+            _lib.check(L.nd_peer_set_staging(self._h, local_bytes, staging_bytes), "nd_peer_set_staging")
+            _lib.check(L.nd_peer_set_mode(self._h, _lib.ND_PEER_PUSH), "nd_peer_set_mode")
+        self._local_bytes = self.n_padded * elem_bytes
         self._raw = _RawDeviceBuffer(self._ptr, self.nbytes)
         self._bytes = torch.as_tensor(self._raw, device=self.device)
 
     def local(self, dtype=torch.float32) -> torch.Tensor:
-        return self._bytes.view(dtype)
+        return self._bytes[: self._local_bytes].view(dtype)
 
     def peer_view(self, w: int, dtype=torch.float32) -> torch.Tensor:
         """Rank w's buffer as mapped into this process (tests / debugging)."""
         p = ctypes.c_void_p()
         _lib.check(_lib.load().nd_peer_buffer(self._h, w, ctypes.byref(p)), "nd_peer_buffer")
-        raw = _RawDeviceBuffer(p.value, self.nbytes)
+        raw = _RawDeviceBuffer(p.value, self._local_bytes)
         t = torch.as_tensor(raw, device=self.device).view(dtype)
         t._nd_keepalive = (raw, self)
         return t
@@ -207,6 +224,13 @@ class PeerContext:
         ms = ctypes.c_float()
         _lib.check(_lib.load().nd_peer_last_ms(self._h, ctypes.byref(ms)), "nd_peer_last_ms")
         return float(ms.value)
+
+    def last_ms2(self):
+        """(total, wait) device milliseconds of the last outer_sync: `wait` is the first flag barrier, i.e.
+        the time spent waiting for the slowest worker to arrive."""
+        tot, wait = ctypes.c_float(), ctypes.c_float()
+        _lib.check(_lib.load().nd_peer_last_ms2(self._h, ctypes.byref(tot), ctypes.byref(wait)), "nd_peer_last_ms2")
+        return float(tot.value), float(wait.value)
 
     def gather_shards(self, shard: torch.Tensor) -> torch.Tensor:
         """Collective over the torch group: contiguous shards -> the full flat buffer."""

@@ -39,7 +39,7 @@ def test_binding_covers_every_declared_symbol():
 
 def test_version_and_scratch_size():
     L = _lib.load()
-    assert L.nd_version() >= 100
+    assert L.nd_version() >= 200
     assert 0 < L.nd_scratch_bytes() < (1 << 20)
 
 

@@ -58,20 +58,24 @@ def test_outer_step_drop_in_w1(golden_dir):
     assert len(sd["state"]) == len(params)
 
 
-def test_inner_step_drop_in(golden_dir):
+@pytest.mark.parametrize("grad_buffer", ["autograd", "flat"])
+def test_inner_step_drop_in(golden_dir, grad_buffer):
     z = np.load(os.path.join(golden_dir, "inner.npz"))
-    model, inner, outer, d = _make(z, warmup_steps=2, total_steps=10)
+    model, inner, outer, d = _make(z, warmup_steps=2, total_steps=10, grad_buffer=grad_buffer)
     params = list(model.parameters())
+    flat = grad_buffer == "flat"
+    assert d.grad_buffer == grad_buffer
     for s in range(6):
         assert inner.param_groups[0]["lr"] == pytest.approx(float(z[f"lr_s{s}"]), rel=1e-12)
         off = 0
         g = z[f"grad_s{s}"]
         for i, p in enumerate(params):
             gi = torch.from_numpy(g[off:off + p.numel()]).reshape(p.shape).cuda()
-            if s % 2 == 0:
+            if flat and s % 2 == 0:
                 p.grad.copy_(gi)            # autograd accumulating into the flat views
             else:
-                p.grad = gi                 # a caller that replaced .grad (set_to_none style)
+                assert flat or p.grad is None   # default mode: no gradient outlives a step (diloco.py:60)
+                p.grad = gi                 # what autograd does when .grad is None; or a caller that replaced it
             off += p.numel()
         d.inner_step()
         assert float(d.last_grad_norm) == pytest.approx(float(z[f"total_norm_s{s}"]), rel=2e-6)
@@ -80,8 +84,47 @@ def test_inner_step_drop_in(golden_dir):
                          (_flat([inner.state[p]["exp_avg_sq"] for p in params]), "exp_avg_sq")):
             want = z[f"{key}_s{s}"]
             np.testing.assert_allclose(host(got), want, rtol=2e-6, atol=1e-6 * np.abs(want).max())
-        assert all(float(p.grad.abs().max()) == 0.0 for p in params)   # zero_grad, fused
+        if flat:
+            assert all(float(p.grad.abs().max()) == 0.0 for p in params)   # zero_grad, fused into the AdamW pass
+        else:
+            assert all(p.grad is None for p in params)                     # zero_grad(set_to_none), diloco.py:60
         assert float(inner.state[params[0]]["step"]) == s + 1
+
+
+@pytest.mark.parametrize("grad_buffer", ["autograd", "flat"])
+def test_inner_step_skips_parameters_without_gradient(grad_buffer):
+    """torch.optim.AdamW leaves a parameter whose .grad is None alone -- no weight decay, no moment decay
+    (torch:optim/adam.py:150-160) -- and clip_grad_norm_ ignores it.  Same here, checked against torch's
+    own CUDA AdamW on a model with an unused branch."""
+    torch.manual_seed(5)
+    mk = lambda: torch.nn.ModuleDict({"a": torch.nn.Linear(24, 40), "unused": torch.nn.Linear(40, 40),
+                                      "b": torch.nn.Linear(40, 3)}).cuda()
+    ours, ref = mk(), mk()
+    ref.load_state_dict(ours.state_dict())
+    fwd = lambda m, x: m["b"](torch.tanh(m["a"](x)))
+    inner = torch.optim.AdamW(ours.parameters(), lr=1e-2)
+    outer = torch.optim.SGD(ours.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(ours, inner, outer, warmup_steps=0, total_steps=1000, grad_buffer=grad_buffer)
+    if grad_buffer == "flat":           # what a partial backward after zero_grad(set_to_none=True) leaves behind
+        for p in ours["unused"].parameters():
+            p.grad = None
+    ref_opt = torch.optim.AdamW(ref.parameters(), lr=1e-2, foreach=True)
+    ref_sched = torch.optim.lr_scheduler.LambdaLR(ref_opt, lambda k: d.scheduler.lr_lambdas[0](k))
+    before = [p.detach().clone() for p in ours["unused"].parameters()]
+    for step in range(3):
+        x = torch.randn(16, 24, device="cuda")
+        fwd(ours, x).square().mean().backward()
+        fwd(ref, x).square().mean().backward()
+        torch.nn.utils.clip_grad_norm_(ref.parameters(), max_norm=1.0)
+        ref_opt.step(); ref_sched.step(); ref_opt.zero_grad()
+        d.inner_step()
+        if grad_buffer == "flat":
+            for p in ours["unused"].parameters():
+                p.grad = None
+    for p, q in zip(ours["unused"].parameters(), before):
+        assert torch.equal(p, q)                                           # untouched, weight decay included
+    for p, q in zip(ours.parameters(), ref.parameters()):
+        torch.testing.assert_close(p, q, rtol=2e-6, atol=1e-7)
 
 
 def test_training_loop_with_autograd():

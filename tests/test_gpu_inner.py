@@ -40,8 +40,15 @@ def test_sumsq_bf16_and_multi_tensor():
     assert float(out) == pytest.approx(O.sumsq(g16.float().cpu().numpy()), rel=2e-6)
     ts = [dev(_rand(s, 20 + i, 0.05)) for i, s in enumerate([128, 7, 16385, 1, 40_000])]
     tab, T, chunks = _lib.make_table([(t,) for t in ts], "cuda")
-    _lib.check(_lib.load().nd_sumsq_mt(tab.data_ptr(), T, chunks, out.data_ptr(), sc.data_ptr(), _lib._stream()))
+    _lib.check(_lib.load().nd_sumsq_mt(tab.data_ptr(), T, chunks, _lib.ND_F32, out.data_ptr(), sc.data_ptr(),
+                                       _lib._stream()))
     want = sum(O.sumsq(host(t)) for t in ts)
+    assert float(out) == pytest.approx(want, rel=2e-6)
+    t16 = [t.to(torch.bfloat16) for t in ts]
+    tab, T, chunks = _lib.make_table([(t,) for t in t16], "cuda")
+    _lib.check(_lib.load().nd_sumsq_mt(tab.data_ptr(), T, chunks, _lib.ND_BF16, out.data_ptr(), sc.data_ptr(),
+                                       _lib._stream()))
+    want = sum(O.sumsq(t.float().cpu().numpy()) for t in t16)
     assert float(out) == pytest.approx(want, rel=2e-6)
 
 
@@ -109,20 +116,35 @@ def test_adamw_vs_reference_golden(golden_dir):
             np.testing.assert_allclose(host(got), want, rtol=2e-6, atol=1e-6 * np.abs(want).max())
 
 
-def test_adamw_multi_tensor_matches_flat():
-    sizes = [128, 7, 16385, 1, 40_000]
-    mk = lambda seed, sc: [dev(_rand(s, seed + i, sc)) for i, s in enumerate(sizes)]
-    ps, gs, ms, vs = mk(0, 0.02), mk(10, 0.01), mk(20, 1e-3), [t.abs() for t in mk(30, 1e-6)]
+@pytest.mark.parametrize("bf16", [False, True])
+@pytest.mark.parametrize("shift", [0, 1])
+def test_adamw_multi_tensor_matches_flat(bf16, shift):
+    """nd_adamw_mt (table-driven, TMA-staged) against nd_adamw tensor by tensor, bit for bit: sizes below,
+    at and above one tile and one chunk, ragged tails, many tiles per CTA; `shift` makes every row
+    unaligned so that the kernel's plain-access path is the one that runs."""
+    sizes = [128, 7, 2048, 16384, 16385, 1, 40_000, 2048 * 148 * 2 * 3 + 12, 5]
+    wd = torch.bfloat16 if bf16 else torch.float32
+    al = (lambda t: unaligned(t, shift)) if shift else (lambda t: t)
+    mk = lambda seed, sc, dt=torch.float32: [al(dev(_rand(s, seed + i, sc)).to(dt)) for i, s in enumerate(sizes)]
+    ps, gs, ms, vs = mk(0, 0.02, wd), mk(10, 0.01, wd), mk(20, 1e-3), [t.abs() for t in mk(30, 1e-6)]
+    ss = torch.full((1,), 9.0, device="cuda")          # norm 3 -> clip coefficient 1/3
     want = []
     for p, g, m, v in zip(ps, gs, ms, vs):
         p2, m2, v2 = p.clone(), m.clone(), v.clone()
-        _lib.adamw(p2, g.clone(), m2, v2, lr=1e-3, step=3, max_norm=1.0)
+        _lib.adamw(p2, g.clone(), m2, v2, lr=1e-3, step=3, sumsq_dev=ss, max_norm=1.0)
         want.append((p2, m2, v2))
+    g0 = [g.clone() for g in gs]
     tab, T, chunks = _lib.make_table(list(zip(ps, gs, ms, vs)), "cuda")
-    _lib.check(_lib.load().nd_adamw_mt(tab.data_ptr(), T, chunks, 1e-3, 0.9, 0.999, 1e-8, 1e-2, 3, None, 1.0, 0,
-                                       _lib._stream()))
-    for (p2, m2, v2), p, m, v in zip(want, ps, ms, vs):
+    code = _lib.ND_BF16 if bf16 else _lib.ND_F32
+    _lib.check(_lib.load().nd_adamw_mt(tab.data_ptr(), T, chunks, code, 1e-3, 0.9, 0.999, 1e-8, 1e-2, 3, ss.data_ptr(),
+                                       1.0, 0, _lib._stream()))
+    for (p2, m2, v2), p, m, v, g, gb in zip(want, ps, ms, vs, gs, g0):
         assert torch.equal(p, p2) and torch.equal(m, m2) and torch.equal(v, v2)
+        assert torch.equal(g, gb)                       # zero_grad = 0: gradients untouched
+    # zero_grad = 1 clears them (the flat-buffer mode of the wrapper relies on it)
+    _lib.check(_lib.load().nd_adamw_mt(tab.data_ptr(), T, chunks, code, 1e-3, 0.9, 0.999, 1e-8, 1e-2, 4, None, 1.0, 1,
+                                       _lib._stream()))
+    assert all(int(torch.count_nonzero(g)) == 0 for g in gs)
 
 
 # ---- bf16 working copy (extension: BASELINE config 2, no reference behaviour) -----------------
