@@ -36,7 +36,10 @@ GOLDEN_CASES = [("golden", m, b) for m, b in [("nccl", 0.002), ("nccl", 64.0), (
 # 214,983,680 parameters: configs[1]) -- at 8 GPUs that is 1.2 M and 26.9 M elements per shard, i.e. 1.2 K and
 # 26 K tiles of the W=8 kernel
 LARGE_CASES = [("large", m, wl) for wl in ("tiny", "llama150m") for m in MODES]
-CASES = GOLDEN_CASES + LARGE_CASES
+# BASELINE configs[0]: what the reference computed around the real tiny Llama with 2 workers (sampled elements,
+# tests/golden/config1_tiny_llama_w2.npz); runs where the job has exactly two workers
+CONFIG1_CASES = [("config1", m, 1.0) for m in ("p2p", "p2p_push", "p2p_offload", "p2p_rep2", "nccl", "nvls", "hybrid")]
+CASES = GOLDEN_CASES + CONFIG1_CASES + LARGE_CASES
 
 
 def _case_id(c):
@@ -126,6 +129,29 @@ def _golden_case(mode, bucket_mb, world, rank):
     ok &= np.array_equal(widen(saved), f32(params))                 # just synced: theta_sync == params
     d.load_state_dict(sd)                     # scatter back into this rank's shard: nothing changes
     ok &= np.array_equal(d.state_dict()["momentum"].numpy(), sd["momentum"].numpy())
+    d.close()
+    return bool(ok)
+
+
+def _config1_case(mode, world, rank):
+    from nanodiloco_b200 import Diloco
+    rep = 2 if mode == "p2p_rep2" else 1
+    if world // rep != 2:
+        raise Skip("config 1 has two workers")
+    z = np.load(os.path.join(GOLDEN, "config1_tiny_llama_w2.npz"))
+    p = torch.nn.Parameter(torch.from_numpy(z["init"].copy()).cuda() + (0.0 if rank == 0 else 1.0))
+    holder = torch.nn.ParameterList([p])
+    inner = torch.optim.AdamW(holder.parameters(), lr=4e-4)
+    outer = torch.optim.SGD(holder.parameters(), lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(holder, inner, outer, 5, 30, **_diloco_kwargs(mode, 0.05, offload_chunk_mb=0.01))
+    ok = np.array_equal(p.detach().cpu().numpy(), z["init"])
+    for r in range(3):
+        with torch.no_grad():
+            p.copy_(torch.from_numpy(z[f"local_r{r}_w{rank // rep}"]))
+        d.outer_step()
+        mom = outer.state_dict()["state"][0]["momentum_buffer"]          # the hook gathers the shards
+        ok &= np.array_equal(p.detach().cpu().numpy(), z[f"params_r{r}"])         # two workers: the mean is order-free,
+        ok &= np.array_equal(mom.cpu().numpy(), z[f"mom_r{r}"])                    # so every transport is bit-exact
     d.close()
     return bool(ok)
 
@@ -226,7 +252,12 @@ def _worker(rank, world, store, cases, result_path):
                 raise Skip("needs an even number of GPUs")
             if mode in ("nvls", "hybrid"):
                 import torch.distributed._symmetric_memory as symm   # noqa: F401
-            ok = _golden_case(mode, case[2], world, rank) if kind == "golden" else _large_case(mode, case[2], world, rank)
+            if kind == "golden":
+                ok = _golden_case(mode, case[2], world, rank)
+            elif kind == "config1":
+                ok = _config1_case(mode, world, rank)
+            else:
+                ok = _large_case(mode, case[2], world, rank)
             verdict = "ok" if ok else "mismatch"
         except Skip as e:
             verdict = f"skip: {e}"
