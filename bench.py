@@ -455,12 +455,28 @@ class NvlinkCounters:
 
     def read(self):
         nv = self.nv
-        vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, 0xFFFFFFFF) for fid in self.FIELDS.values()])
-        out = {}
-        for name, v in zip(self.FIELDS, vals):
-            if v.nvmlReturn != 0:
-                raise RuntimeError(f"NVML field {name}: return code {v.nvmlReturn}")
-            out[name] = int(v.value.ullVal) * 1024          # KiB -> bytes
+        if getattr(self, "per_link", None) is None:
+            # some drivers answer the all-links scope, some only per link: settle it on the first read
+            vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, 0xFFFFFFFF) for fid in self.FIELDS.values()])
+            self.per_link = any(v.nvmlReturn != 0 for v in vals)
+        if not self.per_link:
+            vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, 0xFFFFFFFF) for fid in self.FIELDS.values()])
+            bad = [n for n, v in zip(self.FIELDS, vals) if v.nvmlReturn != 0]
+            if bad:
+                raise RuntimeError(f"NVML NVLink throughput fields {bad}: not available")
+            return {n: int(v.value.ullVal) * 1024 for n, v in zip(self.FIELDS, vals)}          # KiB -> bytes
+        out = {n: 0 for n in self.FIELDS}
+        seen = 0
+        for link in range(18):
+            vals = nv.nvmlDeviceGetFieldValues(self.h, [(fid, link) for fid in self.FIELDS.values()])
+            if any(v.nvmlReturn != 0 for v in vals):
+                continue
+            seen += 1
+            for n, v in zip(self.FIELDS, vals):
+                out[n] += int(v.value.ullVal) * 1024
+        if not seen:
+            raise RuntimeError("NVML NVLink throughput counters: return code 3 (NOT_SUPPORTED) for the all-links scope "
+                               "and for every link -- this driver/VM does not expose them")
         return out
 
 
@@ -615,11 +631,15 @@ def native_arm(args):
         def step(first=False):
             nctx.outer_sync(master, mom, first_step=first, **hyper)
     else:
-        local = (master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)).to(wdtype)
         ctx = SyncContext(world, rank, bucket_elems=int(args.bucket_mb * (1 << 20)) // 4, n_streams=args.streams,
-                          device=dev)
+                          device=dev, ag_comm=not args.nccl_single_comm)
+        if world > 1 and not args.nccl_no_register:
+            local, pg = ctx.alloc(n), ctx.alloc(n)       # NCCL-allocated, registered: collectives may run in-switch
+        else:
+            local = torch.empty(n, device=dev, dtype=wdtype)
+            pg = torch.empty(n, device=dev) if world > 1 else None
+        local.copy_((master + torch.empty(n, device=dev).normal_(0, 1e-3, generator=gl)).to(wdtype))
         mom = torch.zeros(ctx.shard_elems(n), device=dev)
-        pg = torch.empty(n, device=dev) if world > 1 else None
 
         def step(first=False):
             if world == 1:
@@ -734,6 +754,35 @@ def native_arm(args):
                     "algorithmic_bytes_per_launch": nvl_bytes, "kernel_ms": ms,
                     "hbm": {"achieved": achieved, "peak": peak, "frac": achieved / peak, "peak_source": peak_src,
                             "algorithmic_bytes_per_launch": kern_bytes}}
+
+    # ---- NCCL pipeline: per-bucket stage timeline and bus bandwidth of one extra (profiled) step -------
+    nccl_timeline = None
+    if mode == "nccl" and world > 1:
+        ctx.set_profiling(True)
+        step()
+        torch.cuda.synchronize()
+        rows = ctx.timeline()
+        ctx.set_profiling(False)
+        if rows:
+            blen = min(ctx.bucket, n)
+            wire = 4.0 * blen * (world - 1) / world               # bytes each rank sends per collective per bucket
+            dur = lambda k: [r[k][1] - r[k][0] for r in rows]
+            med = lambda xs: statistics.median(xs) if xs else None
+            span = lambda k: (min(r[k][0] for r in rows), max(r[k][1] for r in rows))
+            busy = lambda k: sum(dur(k))
+            total_ms = max(r["refresh"][1] for r in rows)
+            nccl_timeline = {
+                "buckets": len(rows), "bucket_elems": blen, "total_ms": total_ms,
+                "median_ms": {k: med(dur(k)) for k in ("k1", "rs", "k2", "ag", "refresh")},
+                "sum_ms": {k: busy(k) for k in ("k1", "rs", "k2", "ag", "refresh")},
+                "span_ms": {k: span(k) for k in ("k1", "rs", "k2", "ag", "refresh")},
+                "rs_bus_gbs_median": wire / (med(dur("rs")) * 1e-3) / 1e9 if med(dur("rs")) else None,
+                "ag_bus_gbs_median": wire / (med(dur("ag")) * 1e-3) / 1e9 if med(dur("ag")) else None,
+                "note": "event times on the issuing streams; a stage's duration includes waiting for the stream's "
+                        "previous op and, for NCCL kernels, for the communicator's previous collective",
+                "first_buckets": rows[:6],
+                "ag_comm": ctx.ag_comm, "registered_buffers": not args.nccl_no_register,
+            }
 
     # ---- NVLink bytes per step from the NVML counters (per direction, worst rank) -----------------
     nvlink_measured = None
@@ -924,7 +973,7 @@ def native_arm(args):
             "dtype": "f32" if not bf16 else "f32 master/momentum, bf16 working copy", "data": "synthetic",
             "config": workload_config(args, n_real, len(shapes), world),
             "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
-            "parity_check": parity, "nvlink_measured": nvlink_measured,
+            "parity_check": parity, "nvlink_measured": nvlink_measured, "nccl_timeline": nccl_timeline,
             "p2p_exchange": pctx_exchange,
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
@@ -969,6 +1018,8 @@ def main():
     ap.add_argument("--no-tokens", action="store_true", help="skip the tokens/s training-loop measurement")
     ap.add_argument("--tokens-inner-steps", type=int, default=10)
     ap.add_argument("--no-extras", action="store_true", help="skip the inner-step and reference-GPU-path timings")
+    ap.add_argument("--nccl-single-comm", action="store_true", help="--sync nccl: all-gathers share the reduce-scatters' communicator")
+    ap.add_argument("--nccl-no-register", action="store_true", help="--sync nccl: plain torch memory instead of ncclMemAlloc + ncclCommRegister")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of one extra step")
     ap.add_argument("--parity-elems", type=int, default=1 << 24, help="elements per rank the parity check compares")
     ap.add_argument("--p2p-exchange", choices=["auto", "pull", "push"], default="auto",

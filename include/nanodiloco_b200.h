@@ -227,6 +227,29 @@ int nd_sync_ctx_create(const char unique_id_host[ND_UNIQUE_ID_BYTES], int world,
                        int64_t bucket_elems, int n_streams, nd_sync_ctx** out);
 int nd_sync_ctx_destroy(nd_sync_ctx* ctx);
 
+/* Optional: a SECOND communicator used for the all-gathers only.  NCCL runs one communicator's
+ * collectives in issue order, so with a single one AG(b) queues behind RS(b+1); with two, the
+ * all-gather of bucket b and the reduce-scatter of bucket b+1 are independent NCCL kernels.
+ * Collective over the ranks; `unique_id_host` is a second id from nd_nccl_unique_id on rank 0. */
+int nd_sync_ctx_add_ag_comm(nd_sync_ctx* ctx, const char unique_id_host[128]);
+
+/* Buffers from NCCL's own allocator (ncclMemAlloc: CUDA VMM memory NCCL can bind to the NVSwitch
+ * multicast object) and their registration with the context's communicators (ncclCommRegister), so
+ * that reduce-scatter / all-gather may run in-switch (NVLS) straight on the user buffers instead of
+ * staging through NCCL's internal ones.  These replace nothing in the reference -- its buffers are
+ * ordinary torch tensors (diloco.py:48-49) -- they are how the pipeline reaches the fabric's peak.
+ * Register `local` and `pg` after nd_sync_ctx_create (and nd_sync_ctx_add_ag_comm). */
+int nd_nccl_mem_alloc(size_t bytes, void** dev_ptr_out);
+int nd_nccl_mem_free(void* dev_ptr);
+int nd_sync_register(nd_sync_ctx* ctx, void* buf, size_t bytes);
+
+/* Per-bucket stage timeline of the LAST nd_outer_sync (row f4 of the scope table: per-bucket
+ * counters).  With profiling on, every bucket records 7 CUDA events; nd_sync_timeline returns, per
+ * bucket, milliseconds since the call started for: K1 start, K1 end, reduce-scatter end, K2 start,
+ * K2 end, all-gather end, master-refresh end (rows_out: n_rows x 7 floats; waits for the sync). */
+int nd_sync_set_profiling(nd_sync_ctx* ctx, int on);
+int nd_sync_timeline(nd_sync_ctx* ctx, float* rows_out, int64_t cap_rows, int64_t* n_rows_out);
+
 /* Elements of the padded flat parameter space for n real elements (multiple of
  * bucket size boundaries so that every bucket splits into `world` equal,
  * 16-byte-aligned shards), and the number of elements of sharded state

@@ -49,6 +49,12 @@ SIGNATURES = {
     "nd_nccl_unique_id": (_c_i, [ctypes.c_char_p]),
     "nd_sync_ctx_create": (_c_i, [ctypes.c_char_p, _c_i, _c_i, _c_i64, _c_i, ctypes.POINTER(_c_p)]),
     "nd_sync_ctx_destroy": (_c_i, [_c_p]),
+    "nd_sync_ctx_add_ag_comm": (_c_i, [_c_p, ctypes.c_char_p]),
+    "nd_nccl_mem_alloc": (_c_i, [ctypes.c_size_t, ctypes.POINTER(_c_p)]),
+    "nd_nccl_mem_free": (_c_i, [_c_p]),
+    "nd_sync_register": (_c_i, [_c_p, _c_p, ctypes.c_size_t]),
+    "nd_sync_set_profiling": (_c_i, [_c_p, _c_i]),
+    "nd_sync_timeline": (_c_i, [_c_p, ctypes.POINTER(_c_f), _c_i64, ctypes.POINTER(_c_i64)]),
     "nd_sync_padded_elems": (_c_i64, [_c_p, _c_i64]),
     "nd_sync_shard_elems": (_c_i64, [_c_p, _c_i64]),
     "nd_sync_bucket_elems": (_c_i64, [_c_p]),

@@ -18,6 +18,7 @@
 
 #include <cstdlib>
 #include <cstring>
+#include <utility>
 #include <vector>
 
 #include "nd_common.cuh"
@@ -40,6 +41,11 @@ struct NcclApi {
     int (*ReduceScatter)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
+    // optional (NCCL >= 2.19): buffers NCCL can map into the switch / use without staging copies
+    int (*MemAlloc)(void**, size_t) = nullptr;
+    int (*MemFree)(void*) = nullptr;
+    int (*CommRegister)(ncclComm_t, void*, size_t, void**) = nullptr;
+    int (*CommDeregister)(ncclComm_t, void*) = nullptr;
 };
 
 static NcclApi g_nccl;
@@ -67,6 +73,10 @@ static int load_nccl() {
     ND_SYM(AllGather, "ncclAllGather");
     ND_SYM(GetErrorString, "ncclGetErrorString");
 #undef ND_SYM
+    *reinterpret_cast<void**>(&g_nccl.MemAlloc) = dlsym(h, "ncclMemAlloc");
+    *reinterpret_cast<void**>(&g_nccl.MemFree) = dlsym(h, "ncclMemFree");
+    *reinterpret_cast<void**>(&g_nccl.CommRegister) = dlsym(h, "ncclCommRegister");
+    *reinterpret_cast<void**>(&g_nccl.CommDeregister) = dlsym(h, "ncclCommDeregister");
     g_nccl.handle = h;
     return ND_OK;
 }
@@ -84,6 +94,12 @@ using namespace nd;
 
 struct nd_sync_ctx {
     ncclComm_t comm = nullptr;
+    ncclComm_t comm_ag = nullptr;     // optional second communicator: all-gathers stop queueing behind reduce-scatters
+    std::vector<std::pair<ncclComm_t, void*>> registrations;   // (communicator, handle) of registered user buffers
+    bool profile = false;             // record the per-bucket stage events below
+    std::vector<cudaEvent_t> stage_events;   // kStageEvents per bucket
+    int64_t profiled_buckets = 0;
+    static constexpr int kStageEvents = 7;   // K1 start/end, RS end, K2 start/end, AG end, refresh end
     int world = 1, rank = 0;
     int64_t bucket = 0;  // elements per bucket, multiple of 4*world
     int n_streams = 1;
@@ -160,8 +176,68 @@ int nd_sync_ctx_destroy(nd_sync_ctx* c) {
     if (c->fork) cudaEventDestroy(c->fork);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
+    for (auto& r : c->registrations)
+        if (g_nccl.CommDeregister) g_nccl.CommDeregister(r.first, r.second);
+    for (auto e : c->stage_events) if (e) cudaEventDestroy(e);
+    if (c->comm_ag) g_nccl.CommDestroy(c->comm_ag);
     if (c->comm) g_nccl.CommDestroy(c->comm);
     delete c;
+    return ND_OK;
+}
+
+int nd_sync_ctx_add_ag_comm(nd_sync_ctx* c, const char unique_id_host[ND_UNIQUE_ID_BYTES]) {
+    if (!c) return set_error(ND_ESTATE, "nd_sync_ctx_add_ag_comm: null context");
+    if (c->world == 1 || c->comm_ag) return ND_OK;
+    if (!unique_id_host) return set_error(ND_EINVAL, "nd_sync_ctx_add_ag_comm: null unique id");
+    ncclUniqueId id;
+    memcpy(id.internal, unique_id_host, ND_UNIQUE_ID_BYTES);
+    ND_NCCL(g_nccl.CommInitRank(&c->comm_ag, c->world, id, c->rank));
+    return ND_OK;
+}
+
+int nd_nccl_mem_alloc(size_t bytes, void** dev_ptr_out) {
+    if (!dev_ptr_out || bytes == 0) return set_error(ND_EINVAL, "nd_nccl_mem_alloc: bad argument");
+    if (int rc = load_nccl()) return rc;
+    if (!g_nccl.MemAlloc) return set_error(ND_ENCCL, "this libnccl has no ncclMemAlloc (needs NCCL >= 2.19)");
+    ND_NCCL(g_nccl.MemAlloc(dev_ptr_out, bytes));
+    return ND_OK;
+}
+
+int nd_nccl_mem_free(void* dev_ptr) {
+    if (!dev_ptr) return ND_OK;
+    if (!g_nccl.MemFree) return set_error(ND_ENCCL, "this libnccl has no ncclMemFree");
+    ND_NCCL(g_nccl.MemFree(dev_ptr));
+    return ND_OK;
+}
+
+int nd_sync_register(nd_sync_ctx* c, void* buf, size_t bytes) {
+    if (!c || !buf || bytes == 0) return set_error(ND_EINVAL, "nd_sync_register: bad argument");
+    if (c->world == 1) return ND_OK;
+    if (!g_nccl.CommRegister) return set_error(ND_ENCCL, "this libnccl has no ncclCommRegister (needs NCCL >= 2.19)");
+    for (ncclComm_t comm : {c->comm, c->comm_ag}) {
+        if (!comm) continue;
+        void* h = nullptr;
+        ND_NCCL(g_nccl.CommRegister(comm, buf, bytes, &h));
+        c->registrations.emplace_back(comm, h);
+    }
+    return ND_OK;
+}
+
+int nd_sync_set_profiling(nd_sync_ctx* c, int on) {
+    if (!c) return set_error(ND_ESTATE, "nd_sync_set_profiling: null context");
+    c->profile = on != 0;
+    return ND_OK;
+}
+
+int nd_sync_timeline(nd_sync_ctx* c, float* rows_out, int64_t cap_rows, int64_t* n_rows_out) {
+    if (!c || !n_rows_out) return set_error(ND_EINVAL, "nd_sync_timeline: null argument");
+    *n_rows_out = c->profiled_buckets;
+    if (!rows_out || c->profiled_buckets == 0) return ND_OK;
+    ND_CUDA(cudaEventSynchronize(c->t1));
+    const int K = nd_sync_ctx::kStageEvents;
+    for (int64_t b = 0; b < c->profiled_buckets && b < cap_rows; ++b)
+        for (int k = 0; k < K; ++k)
+            ND_CUDA(cudaEventElapsedTime(&rows_out[b * K + k], c->t0, c->stage_events[b * K + k]));
     return ND_OK;
 }
 
@@ -210,6 +286,20 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
     // is on the wire while K2(b) runs (NCCL executes one communicator's collectives in
     // issue order, whatever stream they are on).
     const int64_t nb = (n_padded + c->bucket - 1) / c->bucket;
+    constexpr int KE = nd_sync_ctx::kStageEvents;
+    c->profiled_buckets = 0;
+    if (c->profile) {
+        while ((int64_t)c->stage_events.size() < nb * KE) {
+            cudaEvent_t e;
+            ND_CUDA(cudaEventCreate(&e));
+            c->stage_events.push_back(e);
+        }
+        c->profiled_buckets = nb;
+    }
+    auto mark = [&](int64_t b, int k, cudaStream_t s) -> int {
+        if (c->profile) ND_CUDA(cudaEventRecord(c->stage_events[b * KE + k], s));
+        return ND_OK;
+    };
     auto bucket_len = [&](int64_t b) {
         const int64_t off = b * c->bucket;
         return (n_padded - off < c->bucket) ? (n_padded - off) : c->bucket;  // multiple of 4*W
@@ -218,12 +308,15 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
         const int64_t off = b * c->bucket, len = bucket_len(b), slice = len / W;
         cudaStream_t s = c->streams[b % c->n_streams];
         float* pb = pg + off;
-        int rc = nd_pseudo_grad(master + off, local + off, ND_F32, pb, len, reinterpret_cast<nd_stream_t>(s));
+        int rc;
+        if ((rc = mark(b, 0, s))) return rc;
+        rc = nd_pseudo_grad(master + off, local + off, ND_F32, pb, len, reinterpret_cast<nd_stream_t>(s));
         if (rc) return rc;
+        if ((rc = mark(b, 1, s))) return rc;
         // the reduced slice lands in place of our own slice of the staging buffer
         ND_NCCL(g_nccl.ReduceScatter(pb, pb + (int64_t)c->rank * slice, (size_t)slice, ncclFloat32, ncclSum,
                                      c->comm, s));
-        return ND_OK;
+        return mark(b, 2, s);
     };
     auto stage_b = [&](int64_t b) -> int {
         const int64_t off = b * c->bucket, len = bucket_len(b), slice = len / W;
@@ -231,14 +324,24 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
         // every full bucket contributes bucket/W elements to this rank's shard
         const int64_t shard_off = b * (c->bucket / W);
         cudaStream_t s = c->streams[b % c->n_streams];
-        int rc = nd_outer_nesterov(master + mine, mom_shard + shard_off, pg + mine, local + mine, ND_F32, slice,
-                                   (float)W, lr, mu, dampening, wd, nesterov, first_step, nullptr, nullptr,
-                                   reinterpret_cast<nd_stream_t>(s));
+        int rc;
+        if ((rc = mark(b, 3, s))) return rc;
+        rc = nd_outer_nesterov(master + mine, mom_shard + shard_off, pg + mine, local + mine, ND_F32, slice,
+                               (float)W, lr, mu, dampening, wd, nesterov, first_step, nullptr, nullptr,
+                               reinterpret_cast<nd_stream_t>(s));
         if (rc) return rc;
-        ND_NCCL(g_nccl.AllGather(local + mine, local + off, (size_t)slice, ncclFloat32, c->comm, s));
-        // master replica refresh: theta_sync <- the gathered parameters (diloco.py:54)
-        ND_CUDA(cudaMemcpyAsync(master + off, local + off, (size_t)len * sizeof(float), cudaMemcpyDeviceToDevice, s));
-        return ND_OK;
+        if ((rc = mark(b, 4, s))) return rc;
+        ND_NCCL(g_nccl.AllGather(local + mine, local + off, (size_t)slice, ncclFloat32,
+                                 c->comm_ag ? c->comm_ag : c->comm, s));
+        if ((rc = mark(b, 5, s))) return rc;
+        // master replica refresh: theta_sync <- the slices other ranks own (diloco.py:54); ours was written by K2
+        if (mine > off)
+            ND_CUDA(cudaMemcpyAsync(master + off, local + off, (size_t)(mine - off) * sizeof(float),
+                                    cudaMemcpyDeviceToDevice, s));
+        if (mine + slice < off + len)
+            ND_CUDA(cudaMemcpyAsync(master + mine + slice, local + mine + slice,
+                                    (size_t)(off + len - mine - slice) * sizeof(float), cudaMemcpyDeviceToDevice, s));
+        return mark(b, 6, s);
     };
     if (nb > 0) {
         int rc = stage_a(0);

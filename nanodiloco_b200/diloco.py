@@ -172,6 +172,7 @@ class Diloco:
             raise NotImplementedError("replicas_per_worker > 1 needs the peer-memory sync (sync='p2p')")
         self._peer = None
         self._nvls = None
+        self._ctx = None
         if self.sync_mode in ("nvls", "hybrid"):
             if wdtype != torch.float32 or offload_master or self.replicas > 1:
                 raise NotImplementedError("sync='nvls' handles an fp32 working copy, resident master, one rank per worker")
@@ -185,9 +186,14 @@ class Diloco:
             self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
                                      device=dev, replicas=self.replicas, exchange=p2p_exchange)
             self._local = self._peer.local(wdtype)[:n]
-        else:
-            if self.sync_mode == "nccl" and wdtype != torch.float32:
+        elif self.sync_mode == "nccl":
+            if wdtype != torch.float32:
                 raise NotImplementedError("the NCCL pipeline handles an fp32 working copy; use sync='p2p'")
+            from .sync import SyncContext
+            self._ctx = SyncContext(W, self.rank, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
+                                    n_streams=n_streams, group=process_group, device=dev)
+            self._local = self._nccl_buffer(n)
+        else:
             self._local = torch.zeros(n, dtype=wdtype, device=dev)
         rehome_(self._params, self._local, self.layout)
 
@@ -226,17 +232,13 @@ class Diloco:
             self._master = self._local.float().clone()
 
         # ---- sharded sync context -------------------------------------------------------------
-        self._ctx = None
         if self._peer is not None or self._nvls is not None:
             lo, hi = (self._peer or self._nvls).shard_range()
             self._mom = torch.zeros(hi - lo, dtype=torch.float32, device=dev)
             self._pg = None
         elif W > 1:
-            from .sync import SyncContext
-            self._ctx = SyncContext(W, self.rank, bucket_elems=int(bucket_mb * (1 << 20)) // 4,
-                                    n_streams=n_streams, group=process_group, device=dev)
             self._mom = torch.zeros(self._ctx.shard_elems(n), dtype=torch.float32, device=dev)
-            self._pg = torch.empty(n, dtype=torch.float32, device=dev)
+            self._pg = self._nccl_buffer(n)
         else:
             self._mom = torch.zeros(n, dtype=torch.float32, device=dev)
             self._pg = None
@@ -314,6 +316,18 @@ class Diloco:
         """(group, start, end) ranges of consecutive trainable tensors per param group (flat.trainable_runs)."""
         groups = optimizer.param_groups
         return [(groups[gi], s, e) for gi, s, e in trainable_runs(self.layout, [g["params"] for g in groups])]
+
+    def _nccl_buffer(self, n: int) -> torch.Tensor:
+        """fp32 buffer the NCCL pipeline exchanges: from NCCL's allocator and registered with the
+        communicators (so the collectives may run in-switch on it) unless ND_NCCL_REGISTER=0 or this NCCL
+        cannot; then ordinary torch memory, which NCCL stages through its own buffers."""
+        if os.environ.get("ND_NCCL_REGISTER", "1") == "1":
+            try:
+                return self._ctx.alloc(n)
+            except _lib.NDError as e:
+                import warnings
+                warnings.warn(f"NCCL buffer registration unavailable ({e}); using unregistered memory")
+        return torch.zeros(n, dtype=torch.float32, device=self.device)
 
     def _attach_grads(self) -> None:
         for p, gv in zip(self._params, self._grad_views):

@@ -10,6 +10,7 @@ and uses per tensor at nanodiloco/diloco/diloco.py:49.
 from __future__ import annotations
 
 import ctypes
+from ctypes import c_int64 as _c_i64
 
 import torch
 import torch.distributed as dist
@@ -45,8 +46,12 @@ def hybrid_index_map(n_padded: int, n_nvls: int, world: int, rank: int, bucket: 
 
 class SyncContext:
     def __init__(self, world: int, rank: int, *, bucket_elems: int, n_streams: int = 2, group=None,
-                 device=None):
+                 device=None, ag_comm=None):
+        """ag_comm: give the all-gathers a communicator of their own (default: on, ND_NCCL_AG_COMM=0 turns
+        it off) so that they do not queue behind the next bucket's reduce-scatter."""
+        import os
         L = _lib.load()
+        self._nccl_bufs = []
         self.world, self.rank, self.group = world, rank, group
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         uid = ctypes.create_string_buffer(_lib.ND_UNIQUE_ID_BYTES)
@@ -63,6 +68,57 @@ class SyncContext:
                                             ctypes.byref(handle)), "nd_sync_ctx_create")
         self._h = handle
         self.bucket = int(L.nd_sync_bucket_elems(self._h))
+        if ag_comm is None:
+            ag_comm = os.environ.get("ND_NCCL_AG_COMM", "1") == "1"
+        self.ag_comm = bool(ag_comm) and world > 1
+        if self.ag_comm:
+            uid2 = ctypes.create_string_buffer(_lib.ND_UNIQUE_ID_BYTES)
+            if rank == 0:
+                _lib.check(L.nd_nccl_unique_id(uid2), "nd_nccl_unique_id")
+            box = [uid2.raw]
+            dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            uid2 = ctypes.create_string_buffer(box[0], _lib.ND_UNIQUE_ID_BYTES)
+            with torch.cuda.device(self.device):
+                _lib.check(L.nd_sync_ctx_add_ag_comm(self._h, uid2), "nd_sync_ctx_add_ag_comm")
+
+    def alloc(self, numel: int, dtype=torch.float32) -> torch.Tensor:
+        """A zeroed device tensor in memory from NCCL's allocator, registered with this context's
+        communicators (nd_nccl_mem_alloc + nd_sync_register): what `local` and `pg` should live in for the
+        reduce-scatter / all-gather to run on them without staging copies.  Freed by close()."""
+        L = _lib.load()
+        nbytes = int(numel) * torch.empty(0, dtype=dtype).element_size()
+        ptr = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(L.nd_nccl_mem_alloc(max(nbytes, 16), ctypes.byref(ptr)), "nd_nccl_mem_alloc")
+            self._nccl_bufs.append(ptr.value)
+            _lib.check(L.nd_sync_register(self._h, ptr.value, max(nbytes, 16)), "nd_sync_register")
+        raw = _RawDeviceBuffer(ptr.value, nbytes)
+        t = torch.as_tensor(raw, device=self.device).view(dtype)
+        t._nd_keepalive = (raw, self)
+        t.zero_()
+        return t
+
+    def set_profiling(self, on: bool) -> None:
+        _lib.check(_lib.load().nd_sync_set_profiling(self._h, int(bool(on))), "nd_sync_set_profiling")
+
+    def timeline(self):
+        """Per-bucket stage times of the last outer_sync (needs set_profiling(True) before it): a list of
+        dicts with milliseconds since the call started -- k1 = pseudo-gradient kernel, rs = reduce-scatter,
+        k2 = shard update, ag = all-gather, refresh = master replica copy -- and each collective's bus GB/s
+        (bytes every rank sends = (W-1)/W of the bucket, over the time that collective took)."""
+        L = _lib.load()
+        n = _c_i64(0)
+        _lib.check(L.nd_sync_timeline(self._h, None, 0, ctypes.byref(n)), "nd_sync_timeline")
+        if n.value == 0:
+            return []
+        buf = (ctypes.c_float * (7 * n.value))()
+        _lib.check(L.nd_sync_timeline(self._h, buf, n.value, ctypes.byref(n)), "nd_sync_timeline")
+        rows = []
+        for b in range(n.value):
+            k1s, k1e, rse, k2s, k2e, age, rfe = buf[7 * b: 7 * b + 7]
+            rows.append({"bucket": b, "k1": (k1s, k1e), "rs": (k1e, rse), "k2": (k2s, k2e), "ag": (k2e, age),
+                         "refresh": (age, rfe)})
+        return rows
 
     def padded_elems(self, n: int) -> int:
         return int(_lib.load().nd_sync_padded_elems(self._h, n))
@@ -105,8 +161,12 @@ class SyncContext:
 
     def close(self) -> None:
         if getattr(self, "_h", None):
-            _lib.load().nd_sync_ctx_destroy(self._h)
+            torch.cuda.synchronize(self.device)
+            _lib.load().nd_sync_ctx_destroy(self._h)     # deregisters the buffers before they are freed
             self._h = None
+            for p in self._nccl_bufs:
+                _lib.load().nd_nccl_mem_free(p)
+            self._nccl_bufs = []
 
     def __del__(self):  # pragma: no cover
         try:

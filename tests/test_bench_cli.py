@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 def test_reference_arm_prints_one_json_line():
     out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "tiny",
-                          "--steps", "2", "--warmup", "1", "--cpu-budget-s", "2"], capture_output=True, text=True,
+                          "--steps", "2", "--warmup", "1"], capture_output=True, text=True,
                          timeout=300, cwd=ROOT)
     assert out.returncode == 0, out.stderr[-2000:]
     lines = [l for l in out.stdout.splitlines() if l.startswith("{")]
@@ -20,6 +20,21 @@ def test_reference_arm_prints_one_json_line():
     assert d["higher_is_better"] is False and d["n_gpus"] == 1 and d["value"] > 0
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
     assert d["e2e"] == {"value": d["value"], "unit": "ms", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+    # measured on the whole tensor list, never scaled from a sample
+    assert d["cpu_baseline"]["whole_workload"] is True and d["cpu_baseline"]["extrapolated"] is False
+    assert d["cpu_baseline"]["sample_elems"] == 9_766_528 and d["partial_workload"] is False
+
+
+def test_reference_arm_on_a_capped_sample_says_so_and_does_not_scale():
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--workload", "tiny",
+                          "--steps", "2", "--warmup", "1", "--cpu-max-elems", "5000000"], capture_output=True,
+                         text=True, timeout=300, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    d = json.loads([l for l in out.stdout.splitlines() if l.startswith("{")][0])
+    cb = d["cpu_baseline"]
+    assert cb["whole_workload"] is False and cb["extrapolated"] is False and cb["sample_elems"] < 5_000_001
+    assert d["partial_workload"] is True and d["config"]["workload"].startswith("SAMPLE of tiny")
+    assert d["value"] == cb["value"]                  # the sample's own time
 
 
 def test_native_arm_refuses_to_run_without_a_gpu():

@@ -1,5 +1,7 @@
 """CPU: host-side logic of the drop-in wrapper (no kernels run)."""
 import math
+import os
+import sys
 import re
 
 import pytest
@@ -132,3 +134,23 @@ def test_product_never_imports_the_oracle():
                 src = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle\b", src, flags=re.M), f
                 assert "nd_oracle" not in src and "libnd_oracle" not in src, f
+
+
+def test_reference_import_names_resolve_to_this_package():
+    """`from nanodiloco import Diloco, main`, `nanodiloco.diloco`, `nanodiloco.training_utils`, `python -m nanodiloco`
+    and `-m nanodiloco.main` (reference nanodiloco/__init__.py:1-4, __main__.py:1-4, scripts/train_modal.py:61)."""
+    import subprocess
+    import nanodiloco
+    import nanodiloco_b200
+    from nanodiloco import Diloco, main
+    from nanodiloco.diloco import Diloco as D2
+    from nanodiloco.diloco.diloco import Diloco as D3
+    from nanodiloco.training_utils import (create_run_name, ddp_setup, get_tokenized_dataset, get_tokenizer,  # noqa: F401
+                                           set_seed_all)
+    assert Diloco is nanodiloco_b200.Diloco is D2 is D3
+    assert callable(main) and callable(nanodiloco.main)            # the function, as in the reference, not the module
+    assert sorted(nanodiloco.__all__) == ["Diloco", "main"]
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for mod in ("nanodiloco", "nanodiloco.main"):
+        out = subprocess.run([sys.executable, "-m", mod, "--help"], capture_output=True, text=True, cwd=root, timeout=300)
+        assert out.returncode == 0 and "--inner-steps" in out.stdout and "--llama-config-file" in out.stdout, out.stderr[-500:]

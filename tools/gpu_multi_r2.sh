@@ -22,7 +22,7 @@ PY
 for w in $WHAT; do case $w in
 tests)
   echo "== pytest sync (world $N)"
-  ND_SYNC_TEST_LOG=$OUT/sync_tests_n%W_$TAG.json timeout 1400 python -m pytest tests/test_gpu_sync.py -q -k "\-$N]" > $OUT/pytest_sync_n${N}_$TAG.log 2>&1
+  ND_SYNC_WORLDS=$N ND_SYNC_TEST_LOG=$OUT/sync_tests_n%W_$TAG.json timeout 1400 python -m pytest tests/test_gpu_sync.py -q > $OUT/pytest_sync_n${N}_$TAG.log 2>&1
   echo "pytest rc=$?"; tail -12 $OUT/pytest_sync_n${N}_$TAG.log; cat $OUT/sync_tests_n${N}_$TAG.json 2>/dev/null | tr -d '\n' | cut -c1-3000; echo;;
 bench)
   run_bench pull 29511 $FAST --sync p2p --p2p-exchange pull
