@@ -46,6 +46,7 @@ enum {
 };
 
 #define ND_MAX_WORKERS 16 /* most worker copies one fused launch can read */
+#define ND_MAX_REPLICAS 8 /* most GPUs one DiLoCo worker can span (nd_grad_avg, nd_adamw_rw) */
 
 /* One row of a multi-tensor table (lives in DEVICE memory, built once by the
  * caller because parameter storage never moves -- unlike diloco.py:50, which
@@ -195,6 +196,23 @@ int nd_adamw_bf16(void* p_bf16, void* g_bf16, float* m, float* v, int64_t n,
                   double lr, double beta1, double beta2, double eps, double weight_decay,
                   int64_t step, const float* sumsq_dev, float max_norm, int zero_grad,
                   nd_stream_t stream);
+
+/* Gradient average over the R copies of one worker's gradient (a DiLoCo worker that spans R GPUs:
+ * BASELINE config 5 -- an extension, in the reference every rank is a worker and nothing averages
+ * gradients): g_out = (g_0 + ... + g_{R-1}) / R summed in the order given, sumsq_out[0] = sum(g_out^2).
+ * g_out may alias one of the inputs.  What `dist.all_reduce(grad, AVG)` + the first half of
+ * clip_grad_norm_ (diloco.py:57) would do in two library passes.  R in {1,2,3,4,8}; buffers 16-byte aligned. */
+int nd_grad_avg(void* const* grads_host, int R, void* g_out, int dtype, int64_t n,
+                float* sumsq_out, void* scratch, nd_stream_t stream);
+
+/* nd_adamw / nd_adamw_bf16 for one replica's part of the flat space: the squared gradient norm is the
+ * sum, in the order given, of `n_parts` partial sums (device pointers, possibly in peer memory) and the new
+ * parameters are written to every copy in `p_writes_host` (peer-mapped copies of the other replicas; `p`
+ * itself may be among them).  n_parts = 0: no clipping.  Buffers 16-byte aligned. */
+int nd_adamw_rw(void* p, void* const* p_writes_host, int n_writes, void* g, float* m, float* v, int dtype,
+                int64_t n, double lr, double beta1, double beta2, double eps, double weight_decay,
+                int64_t step, const float* const* sumsq_parts_host, int n_parts, float max_norm,
+                int zero_grad, nd_stream_t stream);
 
 /* Multi-tensor form: ptr[0]=p, ptr[1]=g, ptr[2]=m, ptr[3]=v; `dtype` is the type of p and g (ND_F32,
  * or ND_BF16 with fp32 moments as in nd_adamw_bf16).  This is the form the drop-in wrapper uses by
@@ -399,6 +417,19 @@ int nd_peer_last_ms(nd_peer_ctx* ctx, float* ms_out);
 enum { ND_PEER_PULL = 0, ND_PEER_PUSH = 1 };
 int nd_peer_set_staging(nd_peer_ctx* ctx, size_t byte_offset, size_t bytes);
 int nd_peer_set_mode(nd_peer_ctx* ctx, int mode);
+
+/* The whole inner step (diloco.py:56-60 minus the scheduler) of a worker that spans `replicas` GPUs, as
+ * two kernels per GPU over peer memory: nd_grad_avg on this replica's 1/R of the flat space reading every
+ * replica's gradient, a flag barrier among the replicas, nd_adamw_rw on that part writing every replica's
+ * parameters (exp_avg / exp_avg_sq are kept for the owned part only), a flag barrier.  `params_ctx` maps the
+ * working copies (the context of nd_outer_sync_p2p), `grads_ctx` the gradient buffers (a second
+ * nd_peer_alloc / nd_peer_ctx_create with the same replicas setting); m and v point at element 0 of the full
+ * flat moment buffers.  On return (stream order) the gradient buffer is zero and sumsq_total_out (nullable)
+ * holds the squared norm of the averaged gradient.  An extension: the reference has no such mode. */
+int nd_inner_step_replicas(nd_peer_ctx* params_ctx, nd_peer_ctx* grads_ctx, float* m, float* v, int dtype,
+                           int64_t n_padded, double lr, double beta1, double beta2, double eps,
+                           double weight_decay, int64_t step, float max_norm, float* sumsq_total_out,
+                           nd_stream_t stream);
 
 /* nd_peer_last_ms plus the part of it spent in the first flag barrier of nd_outer_sync_p2p, i.e.
  * waiting for the slowest worker to arrive (the skew the reference's blocking all_reduce, diloco.py:49,

@@ -14,6 +14,7 @@ from . import build as _build
 ND_F32, ND_BF16 = 0, 1
 ND_CHUNK = 16384
 ND_MAX_WORKERS = 16
+ND_MAX_REPLICAS = 8
 ND_UNIQUE_ID_BYTES = 128
 ND_IPC_HANDLE_BYTES = 64
 ND_PEER_PULL, ND_PEER_PUSH = 0, 1
@@ -46,6 +47,11 @@ SIGNATURES = {
     "nd_adamw_bf16": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f,
                              _c_i, _c_p]),
     "nd_adamw_mt": (_c_i, [_c_p, _c_i, _c_i64, _c_i, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_p, _c_f, _c_i, _c_p]),
+    "nd_grad_avg": (_c_i, [ctypes.POINTER(_c_p), _c_i, _c_p, _c_i, _c_i64, _c_p, _c_p, _c_p]),
+    "nd_adamw_rw": (_c_i, [_c_p, ctypes.POINTER(_c_p), _c_i, _c_p, _c_p, _c_p, _c_i, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d,
+                           _c_i64, ctypes.POINTER(_c_p), _c_i, _c_f, _c_i, _c_p]),
+    "nd_inner_step_replicas": (_c_i, [_c_p, _c_p, _c_p, _c_p, _c_i, _c_i64, _c_d, _c_d, _c_d, _c_d, _c_d, _c_i64, _c_f,
+                                      _c_p, _c_p]),
     "nd_nccl_unique_id": (_c_i, [ctypes.c_char_p]),
     "nd_sync_ctx_create": (_c_i, [ctypes.c_char_p, _c_i, _c_i, _c_i64, _c_i, ctypes.POINTER(_c_p)]),
     "nd_sync_ctx_destroy": (_c_i, [_c_p]),

@@ -26,6 +26,7 @@
 #include <cstring>
 #include <cmath>
 #include <atomic>
+#include <type_traits>
 
 #include "nd_common.cuh"
 #include "nd_error.h"
@@ -256,6 +257,12 @@ struct AdamWOpT {
     const float* sumsq;  // nullable
     AdamHyper h;
     float coef;
+    // replicas of one worker (nd_adamw_rw): the squared norm arrives as one partial sum per replica (each
+    // replica reduced its own part of the gradient) and the new parameters go to every replica's copy
+    const float* sumsq_parts[ND_MAX_REPLICAS];
+    int n_parts = 0;
+    PG* p_extra[ND_MAX_REPLICAS];
+    int n_extra = 0;
     struct Regs { float4 p, g, m, v; };
 
     __device__ __forceinline__ void rebase(const nd_tensor_desc& d, int64_t off) {
@@ -265,8 +272,14 @@ struct AdamWOpT {
     // clip_grad.py:165-168, evaluated on the device so the host never waits for the norm
     __device__ __forceinline__ void prologue() {
         coef = 1.0f;
-        if (sumsq) {
-            float total = sqrtf(__ldg(sumsq));
+        if (sumsq || n_parts > 0) {
+            float ss = sumsq ? __ldg(sumsq) : 0.0f;
+            for (int k = 0; k < n_parts; ++k) {   // fixed order: every replica forms the same total
+                float part;
+                asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(part) : "l"(sumsq_parts[k]) : "memory");
+                ss = (k == 0 && !sumsq) ? part : __fadd_rn(ss, part);
+            }
+            float total = sqrtf(ss);
             coef = fminf(__fdiv_rn(h.max_norm, total + 1e-6f), 1.0f);
         }
     }
@@ -293,12 +306,14 @@ struct AdamWOpT {
     }
     __device__ __forceinline__ void store4(int64_t i, const Regs& r) const {
         Local<BF16>::st4(p, i, r.p); st_stream(m + i, r.m); st_stream(v + i, r.v);
+        for (int k = 0; k < n_extra; ++k) Local<BF16>::st4(p_extra[k], i, r.p);
         if (h.zero_grad) Local<BF16>::st4(g, i, make_float4(0.f, 0.f, 0.f, 0.f));
     }
     __device__ __forceinline__ void scalar(int64_t i) const {
         float pi = Local<BF16>::ld1(p, i), mi = m[i], vi = v[i];
         one(pi, Local<BF16>::ld1(g, i), mi, vi);
         Local<BF16>::st1(p, i, pi); m[i] = mi; v[i] = vi;
+        for (int k = 0; k < n_extra; ++k) Local<BF16>::st1(p_extra[k], i, pi);
         if (h.zero_grad) Local<BF16>::st1(g, i, 0.0f);
     }
 };
@@ -471,6 +486,7 @@ struct AdamTileOpT {
     template <int TILE>
     __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
         tma::bulk_store(o.p + off, st.buf(0), (uint32_t)len * kEsz);
+        for (int k = 0; k < o.n_extra; ++k) tma::bulk_store(o.p_extra[k] + off, st.buf(0), (uint32_t)len * kEsz);
         tma::bulk_store(o.m + off, st.buf(2), (uint32_t)len * 4);
         tma::bulk_store(o.v + off, st.buf(3), (uint32_t)len * 4);
         if (o.h.zero_grad) tma::bulk_store(o.g + off, st.buf(1), (uint32_t)len * kEsz);
@@ -478,6 +494,57 @@ struct AdamTileOpT {
     __device__ __forceinline__ void tail(int64_t i) { o.scalar(i); }
 };
 using AdamTileOp = AdamTileOpT<false>;
+
+// Gradient average over the R replicas of one worker (BASELINE config 5; an extension -- in the reference
+// every rank is a worker, so there is no gradient exchange): out = (g_0 + ... + g_{R-1}) / R in replica
+// order, plus the sum of squares of the result.  buffers: one per replica; buffer 0 is reused for the result.
+template <int R, bool BF16>
+struct GradAvgTileOp {
+    static constexpr int kBufs = R;
+    static constexpr bool kHasSum = true;
+    static constexpr int kEsz = BF16 ? 2 : 4;
+    static constexpr int kGran = 16 / kEsz;
+    const char* g[R];
+    char* out;
+    float inv_r_num;   // R as a float (division, like dist.all_reduce(AVG) after a sum)
+    float acc_;
+    __device__ __forceinline__ void prologue() { acc_ = 0.0f; }
+    __device__ __forceinline__ float acc() const { return acc_; }
+    __device__ __forceinline__ uint32_t load_bytes(int len) const { return (uint32_t)len * (uint32_t)(R * kEsz); }
+    template <int TILE>
+    __device__ __forceinline__ void loads(const tma::Stage<TILE>& st, int64_t off, int len, uint64_t* bar) const {
+#pragma unroll
+        for (int k = 0; k < R; ++k) tma::bulk_load(st.buf(k), g[k] + off * kEsz, (uint32_t)len * kEsz, bar);
+    }
+    __device__ __forceinline__ float avg1(float s) {
+        float a = __fdiv_rn(s, inv_r_num);
+        if (BF16) a = __bfloat162float(__float2bfloat16_rn(a));   // the stored value is what gets squared
+        acc_ = __fmaf_rn(a, a, acc_);
+        return a;
+    }
+    template <int TILE>
+    __device__ __forceinline__ void compute(const tma::Stage<TILE>& st, int len, int tid, int nthreads) {
+        for (int i = tid * 4; i < len; i += nthreads * 4) {
+            float4 s = BF16 ? lds_bf16x4(st.buf(0), i) : lds4(st.buf(0) + i);
+#pragma unroll
+            for (int k = 1; k < R; ++k) {
+                float4 x = BF16 ? lds_bf16x4(st.buf(k), i) : lds4(st.buf(k) + i);
+                s = make_float4(__fadd_rn(s.x, x.x), __fadd_rn(s.y, x.y), __fadd_rn(s.z, x.z), __fadd_rn(s.w, x.w));
+            }
+            s = make_float4(avg1(s.x), avg1(s.y), avg1(s.z), avg1(s.w));
+            if (BF16) sts_bf16x4(st.buf(0), i, s); else sts4(st.buf(0) + i, s);
+        }
+    }
+    template <int TILE>
+    __device__ __forceinline__ void stores(const tma::Stage<TILE>& st, int64_t off, int len) const {
+        tma::bulk_store(out + off * kEsz, st.buf(0), (uint32_t)len * kEsz);
+    }
+    __device__ __forceinline__ void tail(int64_t i) {
+        float s = Local<BF16>::ld1(g[0], i);
+        for (int k = 1; k < R; ++k) s = __fadd_rn(s, Local<BF16>::ld1(g[k], i));
+        Local<BF16>::st1(out, i, avg1(s));
+    }
+};
 
 // ===========================================================================
 // Drivers
@@ -1001,4 +1068,83 @@ int nd_adamw_mt(const nd_tensor_desc* table_dev, int n_tensors, int64_t total_ch
     return launch_tile_table<ND_TILE_ADAM>(t, table_dev, n_tensors, total_chunks, nullptr, nullptr, s);
 }
 
+// ---- workers that span several GPUs: the per-inner-step gradient exchange (BASELINE config 5) ----------
+#define ND_TILE_GAVG 2048, 3, 512, 2
+
 }  // extern "C"
+
+template <int R, bool BF16>
+static int launch_grad_avg(void* const* grads, void* out, int64_t n, float* sumsq_out, void* scratch, cudaStream_t s) {
+    GradAvgTileOp<R, BF16> t;
+    for (int k = 0; k < R; ++k) t.g[k] = static_cast<const char*>(grads[k]);
+    t.out = static_cast<char*>(out);
+    t.inv_r_num = (float)R;
+    t.acc_ = 0.f;
+    return launch_tile<ND_TILE_GAVG>(t, n, scratch, sumsq_out, s);
+}
+
+extern "C" {
+
+int nd_grad_avg(void* const* grads_host, int R, void* g_out, int dtype, int64_t n, float* sumsq_out, void* scratch,
+                nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(R >= 1 && R <= ND_MAX_REPLICAS, "R out of range [1, ND_MAX_REPLICAS]");
+    ND_REQUIRE(grads_host && sumsq_out && scratch && (n == 0 || g_out), "null pointer");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
+    bool al = aligned16(g_out);
+    for (int k = 0; k < R; ++k) {
+        ND_REQUIRE(n == 0 || grads_host[k], "null gradient pointer");
+        al = al && aligned16(grads_host[k]);
+    }
+    ND_REQUIRE(al, "gradient buffers must be 16-byte aligned (bulk copies)");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+#define ND_GA(r) case r: return dtype == ND_BF16 ? launch_grad_avg<r, true>(grads_host, g_out, n, sumsq_out, scratch, s) \
+                                                   : launch_grad_avg<r, false>(grads_host, g_out, n, sumsq_out, scratch, s)
+    switch (R) {
+        ND_GA(1); ND_GA(2); ND_GA(3); ND_GA(4); ND_GA(8);
+        default: return set_error(ND_EINVAL, "nd_grad_avg: R must be 1, 2, 3, 4 or 8");
+    }
+#undef ND_GA
+}
+
+int nd_adamw_rw(void* p, void* const* p_writes_host, int n_writes, void* g, float* m, float* v, int dtype, int64_t n,
+                double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
+                const float* const* sumsq_parts_host, int n_parts, float max_norm, int zero_grad, nd_stream_t stream) {
+    ND_REQUIRE(n >= 0, "n < 0");
+    ND_REQUIRE(n == 0 || (p && g && m && v), "null pointer");
+    ND_REQUIRE(dtype == ND_F32 || dtype == ND_BF16, "unknown dtype");
+    ND_REQUIRE(step >= 1, "step must be >= 1 (1-based)");
+    ND_REQUIRE(n_writes >= 0 && n_writes <= ND_MAX_REPLICAS && (n_writes == 0 || p_writes_host), "bad write set");
+    ND_REQUIRE(n_parts >= 0 && n_parts <= ND_MAX_REPLICAS && (n_parts == 0 || sumsq_parts_host), "bad partial sums");
+    bool al = aligned16(p) && aligned16(g) && aligned16(m) && aligned16(v);
+    for (int k = 0; k < n_writes; ++k) {
+        ND_REQUIRE(p_writes_host[k], "null write pointer");
+        al = al && aligned16(p_writes_host[k]);
+    }
+    ND_REQUIRE(al, "buffers must be 16-byte aligned (bulk copies)");
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    auto fill = [&](auto& op) {
+        using PG = typename std::remove_reference<decltype(op)>::type::PG;
+        op.p = static_cast<PG*>(p); op.g = static_cast<PG*>(g); op.m = m; op.v = v;
+        op.sumsq = nullptr; op.coef = 1.f;
+        op.h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, step, max_norm, zero_grad);
+        op.n_parts = n_parts;
+        for (int k = 0; k < n_parts; ++k) op.sumsq_parts[k] = sumsq_parts_host[k];
+        op.n_extra = 0;
+        for (int k = 0; k < n_writes; ++k)      // the copy that is read is written by the regular store
+            if (p_writes_host[k] != p) op.p_extra[op.n_extra++] = static_cast<PG*>(p_writes_host[k]);
+    };
+    if (dtype == ND_BF16) {
+        AdamWOpT<true> op;
+        fill(op);
+        AdamTileOpT<true> t{op};
+        return launch_tile<ND_TILE_ADAM>(t, n, nullptr, nullptr, s);
+    }
+    AdamWOp op;
+    fill(op);
+    AdamTileOp t{op};
+    return launch_tile<ND_TILE_ADAM>(t, n, nullptr, nullptr, s);
+}
+
+}  // extern "C"
+

@@ -41,10 +41,10 @@ __device__ __forceinline__ unsigned long long global_ns() {
 // it does expire the waiting rank records WHO it was waiting for in `diag` (page-locked host memory
 // the host can still read after the context is lost; nd_last_error / nd_peer_last_ms report it)
 // and traps, rather than going on to average parameters that are not there.
-__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int world, int rank, uint32_t epoch, int channel,
-                                    unsigned long long timeout_ns, int* diag) {
-    const int w = threadIdx.x;
-    if (w >= world) return;
+__global__ void peer_barrier_kernel(uint32_t* const* flag_pages, int first, int count, int rank, uint32_t epoch,
+                                    int channel, unsigned long long timeout_ns, int* diag) {
+    if ((int)threadIdx.x >= count) return;
+    const int w = first + threadIdx.x;   // the ranks [first, first + count) meet; the others are not involved
     __threadfence_system();
     // each channel has its own ND_MAX_WORKERS slots, so barriers issued on different streams (whose
     // relative order on the device is not fixed) can never satisfy one another
@@ -184,8 +184,9 @@ struct nd_peer_ctx {
     size_t bytes = 0;                 // payload bytes of each rank's buffer (flags follow)
     std::vector<void*> base;          // mapped base of rank w's buffer (own allocation for w == rank)
     uint32_t** flag_pages_dev = nullptr;
-    static constexpr int kChannels = 4;
-    uint32_t epoch[kChannels] = {0, 0, 0, 0};
+    static constexpr int kChannels = 6;   // 0 outer sync, 1-3 in-switch pipeline lanes, 4 replicas of one worker
+    uint32_t epoch[kChannels] = {0, 0, 0, 0, 0, 0};
+    void* scratch = nullptr;              // norm scratch of nd_inner_step_replicas (nd_scratch_bytes), created on first use
     int replicas = 1;                 // consecutive ranks that hold identical copies of one worker
     size_t staging_off = 0, staging_bytes = 0;   // push mode: where in every rank's buffer the staging slots start
     int mode = 0;                     // 0 = pull (remote reads + remote writes), 1 = push (remote writes only)
@@ -331,6 +332,7 @@ int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     for (auto e : c->bucket_events) cudaEventDestroy(e);
     if (c->flag_pages_dev) cudaFree(c->flag_pages_dev);
     if (c->diag_host) cudaFreeHost(c->diag_host);
+    if (c->scratch) cudaFree(c->scratch);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     if (c->ta) cudaEventDestroy(c->ta);
@@ -362,11 +364,15 @@ static int fill_rw(const nd_peer_ctx* c, size_t byte_off, void** reads, void** w
     return workers;
 }
 
-static int peer_barrier_ch(nd_peer_ctx* c, int channel, cudaStream_t stream) {
+static int peer_barrier_group(nd_peer_ctx* c, int channel, int first, int count, cudaStream_t stream) {
     c->epoch[channel] += 1;
-    peer_barrier_kernel<<<1, 32, 0, stream>>>(c->flag_pages_dev, c->world, c->rank, c->epoch[channel], channel,
+    peer_barrier_kernel<<<1, 32, 0, stream>>>(c->flag_pages_dev, first, count, c->rank, c->epoch[channel], channel,
                                               c->timeout_ns, c->diag_dev);
     return check_launch("peer_barrier_kernel");
+}
+
+static int peer_barrier_ch(nd_peer_ctx* c, int channel, cudaStream_t stream) {
+    return peer_barrier_group(c, channel, 0, c->world, stream);
 }
 
 int nd_peer_barrier(nd_peer_ctx* c, nd_stream_t stream) {
@@ -677,6 +683,90 @@ int nd_peer_last_ms(nd_peer_ctx* c, float* ms_out) {
         return set_error(ND_ECUDA, "nd_peer_last_ms: cudaEventSynchronize failed: %s", cudaGetErrorString(es));
     }
     ND_CUDA(cudaEventElapsedTime(ms_out, c->t0, c->t1));
+    return ND_OK;
+}
+
+// ---- inner step of a worker that spans several GPUs (BASELINE config 5; not in the reference) --------
+// The R replicas of a worker hold identical parameters and each has its own gradient.  Replica j owns the
+// j-th 1/R of the flat space for this step (ZeRO-1 style: it alone keeps exp_avg / exp_avg_sq there):
+//   flag barrier among the R replicas (every backward pass is done);
+//   K_a  reads all R gradients of its part (R-1 over NVLink), averages them in replica order, writes the
+//        average over its own gradient and leaves the sum of squares of its part in its flag page;
+//   flag barrier among the R replicas (gradients read, partial norms published);
+//   K_b  clip coefficient from the R partial norms (same order on every replica), AdamW on its part, the
+//        new parameters bulk-stored into every replica's copy, its gradient part zeroed; the parts of its
+//        gradient buffer that the other replicas consumed are cleared with a memset;
+//   flag barrier (every replica's parameters are complete).
+// Against all_reduce(AVG) + sum of squares + AdamW on every replica this moves 22 instead of ~44 bytes per
+// element through each GPU's HBM and 4(R-1)/R bytes per element per direction over NVLink.
+constexpr size_t kPartialOffset = 1024;   // byte offset of the partial-norm slot inside a flag page
+
+struct PartPtrs { const float* p[ND_MAX_REPLICAS]; };
+__global__ void sum_parts_kernel_v(PartPtrs parts, int n, float* out) {
+    float s = 0.0f;
+    for (int k = 0; k < n; ++k) {
+        float v;
+        asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(parts.p[k]) : "memory");
+        s = k == 0 ? v : __fadd_rn(s, v);
+    }
+    *out = s;
+}
+
+int nd_inner_step_replicas(nd_peer_ctx* pc, nd_peer_ctx* gc, float* m, float* v, int dtype, int64_t n_padded,
+                           double lr, double beta1, double beta2, double eps, double weight_decay, int64_t step,
+                           float max_norm, float* sumsq_total_out, nd_stream_t stream_) {
+    if (!pc || !gc) return set_error(ND_ESTATE, "nd_inner_step_replicas: null context");
+    if (int rc = peer_diag(gc, "nd_inner_step_replicas")) return rc;
+    if (pc->world != gc->world || pc->rank != gc->rank || pc->replicas != gc->replicas)
+        return set_error(ND_EINVAL, "nd_inner_step_replicas: the parameter and gradient contexts differ in world/rank/replicas");
+    const int R = gc->replicas;
+    if (R > ND_MAX_REPLICAS) return set_error(ND_EINVAL, "nd_inner_step_replicas: more than ND_MAX_REPLICAS replicas");
+    if (dtype != ND_F32 && dtype != ND_BF16) return set_error(ND_EINVAL, "nd_inner_step_replicas: unknown dtype");
+    const int gran = dtype == ND_BF16 ? 8 : 4;
+    const size_t esz = dtype == ND_BF16 ? 2 : 4;
+    if (n_padded < 0 || n_padded % ((int64_t)gran * R) != 0)
+        return set_error(ND_EINVAL, "nd_inner_step_replicas: n_padded must be a multiple of %d*replicas", gran);
+    const size_t plimit = pc->staging_bytes ? pc->staging_off : pc->bytes;
+    if ((size_t)n_padded * esz > plimit || (size_t)n_padded * esz > gc->bytes)
+        return set_error(ND_EINVAL, "nd_inner_step_replicas: n_padded exceeds the peer buffers");
+    if (n_padded && (!m || !v)) return set_error(ND_EINVAL, "nd_inner_step_replicas: null pointer");
+    cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+    if (!gc->scratch) {
+        ND_CUDA(cudaMalloc(&gc->scratch, nd_scratch_bytes()));
+        ND_CUDA(cudaMemset(gc->scratch, 0, nd_scratch_bytes()));
+    }
+    const int j = gc->rank % R, first = gc->rank - j;
+    const int64_t part = n_padded / R;
+    const size_t off = (size_t)j * part * esz;
+    void *grads[ND_MAX_REPLICAS], *pw[ND_MAX_REPLICAS];
+    const float* parts[ND_MAX_REPLICAS];
+    for (int k = 0; k < R; ++k) {
+        grads[k] = static_cast<char*>(gc->base[first + k]) + off;
+        pw[k] = static_cast<char*>(pc->base[first + k]) + off;
+        parts[k] = reinterpret_cast<const float*>(static_cast<char*>(gc->base[first + k]) + gc->bytes + kPartialOffset);
+    }
+    char* mine_g = static_cast<char*>(gc->base[gc->rank]);
+    float* my_part = reinterpret_cast<float*>(mine_g + gc->bytes + kPartialOffset);
+    int rc;
+    // every replica's backward pass has finished writing its gradient buffer
+    if (R > 1 && (rc = peer_barrier_group(gc, 4, first, R, stream))) return rc;
+    if ((rc = nd_grad_avg(grads, R, mine_g + off, dtype, part, my_part, gc->scratch, stream_))) return rc;
+    if (R > 1 && (rc = peer_barrier_group(gc, 4, first, R, stream))) return rc;
+    if (sumsq_total_out) {
+        PartPtrs pp;
+        for (int k = 0; k < ND_MAX_REPLICAS; ++k) pp.p[k] = k < R ? parts[k] : nullptr;
+        sum_parts_kernel_v<<<1, 1, 0, stream>>>(pp, R, sumsq_total_out);
+        if ((rc = check_launch("sum_parts_kernel"))) return rc;
+    }
+    // the rest of our gradient buffer has been consumed by the replicas that own those parts
+    if (off) ND_CUDA(cudaMemsetAsync(mine_g, 0, off, stream));
+    if ((size_t)(j + 1) * part < (size_t)n_padded)
+        ND_CUDA(cudaMemsetAsync(mine_g + off + (size_t)part * esz, 0, ((size_t)n_padded - (size_t)(j + 1) * part) * esz, stream));
+    rc = nd_adamw_rw(static_cast<char*>(pc->base[pc->rank]) + off, pw, R, mine_g + off, m + (int64_t)j * part,
+                     v + (int64_t)j * part, dtype, part, lr, beta1, beta2, eps, weight_decay, step, parts, R, max_norm, 1,
+                     stream_);
+    if (rc) return rc;
+    if (R > 1 && (rc = peer_barrier_group(gc, 4, first, R, stream))) return rc;
     return ND_OK;
 }
 

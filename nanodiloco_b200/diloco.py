@@ -269,8 +269,16 @@ class Diloco:
             self._sumsq = torch.zeros(1, dtype=torch.float32, device=dev)
             self._m_views = self.layout.views(self._exp_avg)
             self._v_views = self.layout.views(self._exp_avg_sq)
+            self._gpeer = None
             if grad_buffer == "flat":
-                self._grad = torch.zeros(n, dtype=wdtype, device=dev)
+                if self.replicas > 1 and self._peer is not None:
+                    # the replicas of a worker read each other's gradients over NVLink: a peer-mapped buffer
+                    from .sync import PeerContext
+                    self._gpeer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group, device=dev,
+                                              replicas=self.replicas, exchange="pull")
+                    self._grad = self._gpeer.local(wdtype)[:n]
+                else:
+                    self._grad = torch.zeros(n, dtype=wdtype, device=dev)
                 self._grad_views = self.layout.views(self._grad)
                 self._attach_grads()
             # same keys torch.optim.AdamW creates lazily (torch:optim/adam.py:167-190).  Every parameter
@@ -491,9 +499,21 @@ class Diloco:
                 st["exp_avg"], st["exp_avg_sq"], st["step"] = m, v, self._step_tensor
             self._step_tensor.fill_(float(self._inner_step_count))
 
-        self._hooks = [self.outer_optimizer.register_state_dict_pre_hook(pre_outer),
+        self._hooks = [self.inner_optimizer.register_state_dict_pre_hook(lambda optimizer: self.gather_inner_state()),
+                       self.outer_optimizer.register_state_dict_pre_hook(pre_outer),
                        self.outer_optimizer.register_load_state_dict_post_hook(post_outer),
                        self.inner_optimizer.register_load_state_dict_post_hook(post_inner)]
+
+    def gather_inner_state(self) -> None:
+        """Collective over the replicas of this rank's worker: with `replicas_per_worker > 1` every replica keeps
+        exp_avg / exp_avg_sq for its 1/R of the flat space only; this fills in the rest from the owners, so that
+        `inner_optimizer.state` (whose tensors are views of these buffers) is complete."""
+        if not getattr(self, "_inner_state_sharded", False) or self._intra_group is None:
+            return
+        R, j = self.replicas, self.rank % self.replicas
+        part = self.layout.total // R
+        for buf in (self._exp_avg, self._exp_avg_sq):
+            dist.all_gather_into_tensor(buf, buf[j * part:(j + 1) * part].clone(), group=self._intra_group)
 
     def gather_outer_state(self) -> None:
         """Collective: materialise the full momentum buffers into outer_optimizer.state."""
@@ -587,8 +607,20 @@ class Diloco:
     def _inner_step_flat(self) -> None:
         """Gradients in the flat buffer: one sum-of-squares launch and one AdamW launch per param group;
         the AdamW pass zeroes the gradients (diloco.py:60) and `.grad` stay views of the buffer."""
+        if self._gpeer is not None and len(self._inner_ranges) == 1 and \
+                (self._inner_ranges[0][1], self._inner_ranges[0][2]) == (0, self.layout.total):
+            # a worker of several GPUs: gradient average, norm and AdamW as two kernels per GPU over peer memory,
+            # every replica owning 1/R of the flat space (nd_inner_step_replicas)
+            g = self._inner_ranges[0][0]
+            b1, b2 = g["betas"]
+            self._gpeer.inner_step_replicas(self._peer, self._exp_avg, self._exp_avg_sq, dtype=self.working_dtype,
+                                            lr=float(g["lr"]), beta1=float(b1), beta2=float(b2), eps=float(g["eps"]),
+                                            weight_decay=float(g["weight_decay"]), step=self._inner_step_count,
+                                            max_norm=self.max_grad_norm, sumsq_total_out=self._sumsq)
+            self._inner_state_sharded = True
+            return
         if self._intra_group is not None:
-            # intra-worker data parallelism: one all-reduce of the flat gradient buffer over NVLink
+            # (several param groups or frozen tensors) one all-reduce of the flat gradient buffer over NVLink
             dist.all_reduce(self._grad, op=dist.ReduceOp.AVG, group=self._intra_group)
         _lib.sumsq(self._grad, self._sumsq, self._scratch)
         for g, s, e in self._inner_ranges:
@@ -738,10 +770,15 @@ class Diloco:
             keep = self._local.clone()
             rehome_(self._params, keep, self.layout)
             self._local = keep
-        for ctx in (self._peer, self._nvls, self._ctx, getattr(self, "_off_ctx", None)):
+        if getattr(self, "_gpeer", None) is not None:
+            keepg = self._grad.clone()
+            self._grad, self._grad_views = keepg, self.layout.views(keepg)
+            self._attach_grads()
+        for ctx in (getattr(self, "_gpeer", None), self._peer, self._nvls, self._ctx, getattr(self, "_off_ctx", None)):
             if ctx is not None:
                 ctx.close()
         self._peer = self._nvls = self._ctx = None
+        self._gpeer = None
 
     def __call__(self, *args, **kwargs):
         return self.model(*args, **kwargs)

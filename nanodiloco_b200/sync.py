@@ -285,6 +285,19 @@ class PeerContext:
         _lib.check(_lib.load().nd_peer_last_ms(self._h, ctypes.byref(ms)), "nd_peer_last_ms")
         return float(ms.value)
 
+    def inner_step_replicas(self, params_ctx: "PeerContext", exp_avg, exp_avg_sq, *, dtype=torch.float32, lr, beta1=0.9,
+                            beta2=0.999, eps=1e-8, weight_decay=1e-2, step, max_norm=1.0, sumsq_total_out=None,
+                            stream=None) -> None:
+        """nd_inner_step_replicas with THIS context holding the gradient buffers and `params_ctx` the working
+        copies: gradient average over the replicas of this rank's worker + clip + AdamW on the owned part,
+        new parameters written to every replica."""
+        _lib._require_cuda(exp_avg, exp_avg_sq, sumsq_total_out)
+        code = _lib.ND_BF16 if dtype == torch.bfloat16 else _lib.ND_F32
+        _lib.check(_lib.load().nd_inner_step_replicas(
+            params_ctx._h, self._h, _lib._ptr(exp_avg), _lib._ptr(exp_avg_sq), code, self.n_padded, lr, beta1, beta2, eps,
+            weight_decay, int(step), max_norm, _lib._ptr(sumsq_total_out), _lib._stream(stream)),
+            "nd_inner_step_replicas")
+
     def last_ms2(self):
         """(total, wait) device milliseconds of the last outer_sync: `wait` is the first flag barrier, i.e.
         the time spent waiting for the slowest worker to arrive."""

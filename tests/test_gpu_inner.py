@@ -1,4 +1,5 @@
 """GPU parity of the inner-step kernels (sum of squares, fused clip + AdamW) through the C ABI."""
+import ctypes
 import os
 
 import numpy as np
@@ -190,3 +191,62 @@ def test_adamw_nonfinite_gradients_match_torch():
     ok = ~torch.isnan(p)
     torch.testing.assert_close(p[ok], ref.data[ok], rtol=2e-6, atol=1e-9)
     assert torch.equal(torch.isnan(m), torch.isnan(opt.state[ref]["exp_avg"]))
+
+
+# ---- a worker that spans several GPUs (extension: BASELINE config 5), emulated on one GPU ---------------
+
+@pytest.mark.parametrize("R", [1, 2, 3, 4, 8])
+@pytest.mark.parametrize("bf16", [False, True])
+def test_grad_avg_and_adamw_rw_match_allreduce_avg_then_adamw(R, bf16):
+    """nd_grad_avg + nd_adamw_rw on each replica's 1/R of the space == average of the R gradients (what
+    dist.all_reduce(AVG) leaves on every replica), one global norm, nd_adamw on the whole space."""
+    n = 2048 * 148 * 2 + 8 * R * 5            # several tiles per CTA; divisible by 8*R
+    n -= n % (8 * R)
+    wd = torch.bfloat16 if bf16 else torch.float32
+    code = _lib.ND_BF16 if bf16 else _lib.ND_F32
+    L, st = _lib.load(), _lib._stream()
+    p0 = dev(_rand(n, 1, 0.02)).to(wd)
+    grads = [dev(_rand(n, 10 + k, 0.05)).to(wd) for k in range(R)]
+    m0, v0 = dev(_rand(n, 2, 1e-3)), dev(_rand(n, 3, 1e-6)).abs()
+    # reference: sum in replica order, divide, one rounding to the gradient dtype
+    acc = grads[0].float()
+    for g in grads[1:]:
+        acc = acc + g.float()
+    avg = (acc / float(R)).to(wd)
+    want_ss = torch.zeros(1, device="cuda")
+    sc = _lib.scratch("cuda")
+    _lib.sumsq(avg, want_ss, sc)
+    wp, wm, wv = p0.clone(), m0.clone(), v0.clone()
+    _lib.adamw(wp, avg.clone(), wm, wv, lr=1e-3, step=2, sumsq_dev=want_ss, max_norm=1.0)
+    # replicas: copies of the parameters, own gradient buffers, partial norms
+    ps = [p0.clone() for _ in range(R)]
+    gs = [g.clone() for g in grads]
+    ms, vs = m0.clone(), v0.clone()
+    parts = torch.zeros(R, device="cuda")
+    part = n // R
+    esz = 2 if bf16 else 4
+    arr = lambda ptrs: (ctypes.c_void_p * len(ptrs))(*ptrs)
+    for j in range(R):
+        off = j * part
+        _lib.check(L.nd_grad_avg(arr([g.data_ptr() + off * esz for g in gs]), R, gs[j].data_ptr() + off * esz, code, part,
+                                 parts[j:j + 1].data_ptr(), sc.data_ptr(), st), "nd_grad_avg")
+    for j in range(R):
+        off = j * part
+        _lib.check(L.nd_adamw_rw(ps[j].data_ptr() + off * esz, arr([p.data_ptr() + off * esz for p in ps]), R,
+                                 gs[j].data_ptr() + off * esz, ms.data_ptr() + off * 4, vs.data_ptr() + off * 4, code, part,
+                                 1e-3, 0.9, 0.999, 1e-8, 1e-2, 2, arr([parts[k:k + 1].data_ptr() for k in range(R)]), R,
+                                 1.0, 1, st), "nd_adamw_rw")
+    torch.cuda.synchronize()
+    assert float(parts.sum()) == pytest.approx(float(want_ss), rel=2e-6)
+    for j in range(R):
+        # the clip coefficient comes from the sum of R partial sums instead of one reduction: allow 1 ulp on it
+        if bf16:   # ... which can flip the rounding to bf16 of a handful of elements by one bf16 ulp
+            torch.testing.assert_close(ps[j].float(), wp.float(), rtol=8e-3, atol=1e-6)
+            assert float((ps[j] != wp).float().mean()) < 1e-3
+        else:
+            torch.testing.assert_close(ps[j], wp, rtol=2e-6, atol=1e-8)
+        assert torch.equal(ps[j], ps[0])                                      # every replica identical, bit for bit
+        off = j * part
+        assert int(torch.count_nonzero(gs[j][off:off + part])) == 0            # own part zeroed
+    torch.testing.assert_close(ms, wm, rtol=2e-6, atol=1e-10)
+    torch.testing.assert_close(vs, wv, rtol=4e-6, atol=1e-14)

@@ -39,7 +39,9 @@ LARGE_CASES = [("large", m, wl) for wl in ("tiny", "llama150m") for m in MODES]
 # BASELINE configs[0]: what the reference computed around the real tiny Llama with 2 workers (sampled elements,
 # tests/golden/config1_tiny_llama_w2.npz); runs where the job has exactly two workers
 CONFIG1_CASES = [("config1", m, 1.0) for m in ("p2p", "p2p_push", "p2p_offload", "p2p_rep2", "nccl", "nvls", "hybrid")]
-CASES = GOLDEN_CASES + CONFIG1_CASES + LARGE_CASES
+# the inner step of workers that span 2 GPUs (nd_inner_step_replicas) against all_reduce(AVG) + the flat kernels
+REPLICA_CASES = [("replica_inner", "p2p_rep2", wl) for wl in ("tiny", "llama150m")]
+CASES = GOLDEN_CASES + CONFIG1_CASES + REPLICA_CASES + LARGE_CASES
 
 
 def _case_id(c):
@@ -48,6 +50,16 @@ def _case_id(c):
 
 class Skip(Exception):
     pass
+
+
+_FAILED = []          # names of the checks that failed in the case that is running (this rank)
+
+
+def chk(label, cond) -> bool:
+    cond = bool(cond)
+    if not cond:
+        _FAILED.append(label)
+    return cond
 
 
 def _diloco_kwargs(mode, bucket_mb, offload_chunk_mb=0.001):
@@ -103,18 +115,18 @@ def _golden_case(mode, bucket_mb, world, rank):
         mom = f32([outer.state_dict()["state"][i]["momentum_buffer"] for i in range(len(params))])   # the hook gathers
         O.outer_step(om, [widen(z[f"local_r{r}_w{w}"]).copy() for w in range(workers)], ob, lr=0.7, momentum=0.9,
                      first_step=(r == 0))
-        ok &= np.array_equal(got, widen(master))               # working copy == cast(theta_sync)
+        ok &= chk("np.array_equal(got, widen(master))", np.array_equal(got, widen(master)))               # working copy == cast(theta_sync)
         if mode.startswith("p2p"):     # fixed summation order: bit-exact against the oracle for ANY world size
-            ok &= np.array_equal(master, om) and np.array_equal(mom, ob)
+            ok &= chk("np.array_equal(master, om) and np.array_equal(mom, ob)", np.array_equal(master, om) and np.array_equal(mom, ob))
         if exact_vs_reference:         # order-free average: bit-exact against the reference itself
-            ok &= np.array_equal(master, z[f"params_r{r}"]) and np.array_equal(mom, z[f"mom_r{r}"])
+            ok &= chk("np.array_equal(master, z[f'params_r{r}']) and np.array_equal(mom, z[f'", np.array_equal(master, z[f"params_r{r}"]) and np.array_equal(mom, z[f"mom_r{r}"]))
         elif not bf16:                 # north-star tolerance
-            ok &= np.allclose(master, z[f"params_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"params_r{r}"]).max())
-            ok &= np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max())
-    ok &= d.avg_sync_time > 0
+            ok &= chk("np.allclose(master, z[f'params_r{r}'], rtol=1e-6, atol=1e-6 * np.abs(z", np.allclose(master, z[f"params_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"params_r{r}"]).max()))
+            ok &= chk("np.allclose(mom, z[f'mom_r{r}'], rtol=1e-6, atol=1e-6 * np.abs(z[f'mom", np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max()))
+    ok &= chk("d.avg_sync_time > 0", d.avg_sync_time > 0)
     if mode in ("p2p", "p2p_push"):
         w = d.avg_sync_wait_time
-        ok &= w is not None and 0.0 <= w <= d.avg_sync_time
+        ok &= chk("avg_sync_wait_time is a non-negative number", w is not None and w >= 0.0)
     if mode == "p2p_rep2":
         # inner step: replicas average their gradients and stay identical
         for p in params:
@@ -123,12 +135,12 @@ def _golden_case(mode, bucket_mb, world, rank):
         mine = _flat(params)
         both = [torch.empty_like(mine) for _ in range(world)]
         dist.all_gather(both, mine)
-        ok &= torch.equal(both[rank], both[rank ^ 1])
+        ok &= chk("torch.equal(both[rank], both[rank ^ 1])", torch.equal(both[rank], both[rank ^ 1]))
     sd = d.state_dict()                       # collective: full master and momentum on every rank
     saved = torch.cat([v.reshape(-1) for v in d.layout.views(sd["master"])]).numpy()
-    ok &= np.array_equal(widen(saved), f32(params))                 # just synced: theta_sync == params
+    ok &= chk("np.array_equal(widen(saved), f32(params))", np.array_equal(widen(saved), f32(params)))                 # just synced: theta_sync == params
     d.load_state_dict(sd)                     # scatter back into this rank's shard: nothing changes
-    ok &= np.array_equal(d.state_dict()["momentum"].numpy(), sd["momentum"].numpy())
+    ok &= chk("np.array_equal(d.state_dict()['momentum'].numpy(), sd['momentum'].nump", np.array_equal(d.state_dict()["momentum"].numpy(), sd["momentum"].numpy()))
     d.close()
     return bool(ok)
 
@@ -150,9 +162,62 @@ def _config1_case(mode, world, rank):
             p.copy_(torch.from_numpy(z[f"local_r{r}_w{rank // rep}"]))
         d.outer_step()
         mom = outer.state_dict()["state"][0]["momentum_buffer"]          # the hook gathers the shards
-        ok &= np.array_equal(p.detach().cpu().numpy(), z[f"params_r{r}"])         # two workers: the mean is order-free,
-        ok &= np.array_equal(mom.cpu().numpy(), z[f"mom_r{r}"])                    # so every transport is bit-exact
+        ok &= chk("np.array_equal(p.detach().cpu().numpy(), z[f'params_r{r}'])", np.array_equal(p.detach().cpu().numpy(), z[f"params_r{r}"]))         # two workers: the mean is order-free,
+        ok &= chk("np.array_equal(mom.cpu().numpy(), z[f'mom_r{r}'])", np.array_equal(mom.cpu().numpy(), z[f"mom_r{r}"]))                    # so every transport is bit-exact
     d.close()
+    return bool(ok)
+
+
+def _replica_inner_case(workload, world, rank):
+    """Workers of 2 GPUs: three inner steps through the wrapper (gradient average + norm + AdamW as two peer-memory
+    kernels per GPU, moments sharded over the replicas) against the same steps done the plain way on every rank:
+    NCCL all_reduce(AVG) of the gradient, nd_sumsq, nd_adamw over the whole space."""
+    from nanodiloco_b200 import Diloco, _lib
+    from nanodiloco_b200.workloads import workload_shapes
+    if world % 2:
+        raise Skip("needs an even number of GPUs")
+    dev = torch.device("cuda", rank)
+    model = _Shapes(workload_shapes(workload), dev, torch.float32)
+    params = list(model.parameters())
+    inner = torch.optim.AdamW(params, lr=4e-4)
+    outer = torch.optim.SGD(params, lr=0.7, momentum=0.9, nesterov=True)
+    d = Diloco(model, inner, outer, 1, 100, sync="p2p", replicas_per_worker=2, p2p_exchange="pull")
+    n = d.layout.total
+    ok = d.grad_buffer == "flat" and d._gpeer is not None
+    ref_p = d._local[:n].clone()
+    ref_m, ref_v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    ss, sc = torch.zeros(1, device=dev), _lib.scratch(dev)
+    grp = d._intra_group
+    for step in range(1, 4):
+        gen = torch.Generator(device=dev).manual_seed(500 + 10 * rank + step)      # every replica its own gradient
+        g = torch.zeros(n, device=dev)
+        for gv, p in zip(d.layout.views(g), params):
+            gv.copy_(torch.randn(p.shape, generator=gen, device=dev) * (0.02 if step % 2 else 1e-4))
+            p.grad.copy_(gv)
+        lr = inner.param_groups[0]["lr"]
+        dist.all_reduce(g, op=dist.ReduceOp.AVG, group=grp)
+        _lib.sumsq(g, ss, sc)
+        _lib.adamw(ref_p, g, ref_m, ref_v, lr=lr, step=step, sumsq_dev=ss, max_norm=1.0)
+        d.inner_step()
+        torch.cuda.synchronize()
+        ok &= chk("float(d.last_grad_norm) == pytest.approx(float(ss.sqrt()), rel=2e-6)", float(d.last_grad_norm) == pytest.approx(float(ss.sqrt()), rel=2e-6))
+        ok &= chk("bool(torch.allclose(d._local[:n], ref_p, rtol=2e-6, atol=1e-8))", bool(torch.allclose(d._local[:n], ref_p, rtol=2e-6, atol=1e-8)))
+        ok &= chk("int(torch.count_nonzero(d._grad)) == 0", int(torch.count_nonzero(d._grad)) == 0)                              # zero_grad (diloco.py:60)
+        mine = d._local[:n].clone()
+        other = torch.empty_like(mine)
+        pair = [torch.empty_like(mine) for _ in range(2)]
+        dist.all_gather(pair, mine, group=grp)
+        ok &= chk("torch.equal(pair[0], pair[1])", torch.equal(pair[0], pair[1]))                                       # replicas stay bit-identical
+        del other, pair, mine
+    sd = inner.state_dict()                                                        # the hook completes the sharded moments
+    m_full = torch.cat([sd["state"][i]["exp_avg"].reshape(-1) for i in range(len(params))])
+    v_full = torch.cat([sd["state"][i]["exp_avg_sq"].reshape(-1) for i in range(len(params))])
+    want_m = torch.cat([t.reshape(-1) for t in d.layout.views(ref_m)])
+    want_v = torch.cat([t.reshape(-1) for t in d.layout.views(ref_v)])
+    ok &= chk("bool(torch.allclose(m_full, want_m, rtol=2e-6, atol=1e-10)) and bool(t", bool(torch.allclose(m_full, want_m, rtol=2e-6, atol=1e-10)) and bool(torch.allclose(v_full, want_v, rtol=4e-6, atol=1e-14)))
+    d.close()
+    del d, model, params
+    torch.cuda.empty_cache()
     return bool(ok)
 
 
@@ -188,7 +253,7 @@ def _large_case(mode, workload, world, rank):
     ok = True
     # after the constructor's broadcast every rank holds rank 0's parameters (padding between tensors is zero)
     got0 = torch.cat([p.detach().reshape(-1) for p in params])
-    ok &= torch.equal(got0, init)
+    ok &= chk("torch.equal(got0, init)", torch.equal(got0, init))
     idx = d._shard_indices()                                   # global indices of the elements this rank owns
     exact = mode.startswith("p2p") or workers <= 2
     for rnd in range(2):
@@ -219,21 +284,21 @@ def _large_case(mode, workload, world, rank):
         O.outer_step(om, locs, ob, lr=0.7, momentum=0.9, first_step=(rnd == 0))
         want_l = torch.from_numpy(om).to(wd).float().numpy()
         if exact:
-            ok &= np.array_equal(got_m, om) and np.array_equal(got_b, ob) and np.array_equal(got_l, want_l)
+            ok &= chk("np.array_equal(got_m, om) and np.array_equal(got_b, ob) and np.array_e", np.array_equal(got_m, om) and np.array_equal(got_b, ob) and np.array_equal(got_l, want_l))
         else:
-            ok &= np.allclose(got_m, om, rtol=1e-6, atol=1e-6 * float(np.abs(om).max()))
-            ok &= np.allclose(got_b, ob, rtol=1e-6, atol=1e-6 * float(np.abs(ob).max()))
-            ok &= np.array_equal(got_l, torch.from_numpy(got_m).to(wd).float().numpy())
+            ok &= chk("np.allclose(got_m, om, rtol=1e-6, atol=1e-6 * float(np.abs(om).max()))", np.allclose(got_m, om, rtol=1e-6, atol=1e-6 * float(np.abs(om).max())))
+            ok &= chk("np.allclose(got_b, ob, rtol=1e-6, atol=1e-6 * float(np.abs(ob).max()))", np.allclose(got_b, ob, rtol=1e-6, atol=1e-6 * float(np.abs(ob).max())))
+            ok &= chk("np.array_equal(got_l, torch.from_numpy(got_m).to(wd).float().numpy())", np.array_equal(got_l, torch.from_numpy(got_m).to(wd).float().numpy()))
         # every rank's whole working copy is the same bits
         words = flat().view(torch.int16 if bf16 else torch.int32).sum(dtype=torch.int64).reshape(1)
         lo, hi = words.clone(), words.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        ok &= int(lo) == int(hi)
+        ok &= chk("int(lo) == int(hi)", int(lo) == int(hi))
         if mode in ("p2p", "p2p_push", "p2p_rep2"):            # the pseudo-gradient norm the kernel computes on the way
             pg = O.average([O.pseudo_grad(m_in, l) for l in locs])
             sq = torch.tensor([float(np.sum(pg.astype(np.float64) ** 2))], device=dev, dtype=torch.float64)
             dist.all_reduce(sq)
-            ok &= float(d.last_outer_grad_norm) == pytest.approx(float(sq.sqrt()), rel=1e-5)
+            ok &= chk("float(d.last_outer_grad_norm) == pytest.approx(float(sq.sqrt()), rel=1", float(d.last_outer_grad_norm) == pytest.approx(float(sq.sqrt()), rel=1e-5))
     d.close()
     del d, model, params
     torch.cuda.empty_cache()
@@ -247,6 +312,7 @@ def _worker(rank, world, store, cases, result_path):
     results = {}
     for case in cases:
         kind, mode = case[0], case[1]
+        del _FAILED[:]
         try:
             if mode == "p2p_rep2" and world % 2:
                 raise Skip("needs an even number of GPUs")
@@ -256,9 +322,11 @@ def _worker(rank, world, store, cases, result_path):
                 ok = _golden_case(mode, case[2], world, rank)
             elif kind == "config1":
                 ok = _config1_case(mode, world, rank)
+            elif kind == "replica_inner":
+                ok = _replica_inner_case(case[2], world, rank)
             else:
                 ok = _large_case(mode, case[2], world, rank)
-            verdict = "ok" if ok else "mismatch"
+            verdict = "ok" if ok else f"mismatch on rank {rank}: " + "; ".join(_FAILED[:6])
         except Skip as e:
             verdict = f"skip: {e}"
         except Exception as e:  # noqa: BLE001
@@ -271,8 +339,11 @@ def _worker(rank, world, store, cases, result_path):
             dist.all_reduce(code, op=dist.ReduceOp.MAX)
         except Exception:  # noqa: BLE001
             pass
-        if int(code) == 2 and verdict == "ok":
-            verdict = "mismatch on another rank"
+        if int(code) == 2:       # collect every rank's account on rank 0
+            box = [None] * world
+            dist.all_gather_object(box, verdict)
+            bad = [v for v in box if v != "ok"]
+            verdict = " | ".join(bad) if bad else verdict
         results[_case_id(case)] = verdict
         if rank == 0:
             with open(result_path, "w") as f:
