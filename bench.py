@@ -334,6 +334,63 @@ def _reference_gpu_outer_ms(torch, dist, dev, shapes, world):
             "NCCL all_reduce(AVG) per tensor, foreach SGD, clone + D2H; wall ms, max over ranks, best of 2"}
 
 
+def _replica_inner_ms(torch, dist, _lib, dev, pctx, n, world, rank, replicas, peak, K=10):
+    """One inner step of workers that span `replicas` GPUs (BASELINE configs[4]): nd_inner_step_replicas (gradient
+    average + norm + AdamW as two peer-memory kernels per GPU) against the plain way on the same buffers (NCCL
+    all_reduce(AVG) inside the worker, nd_sumsq, nd_adamw with fused zero-grad).  Device ms, max over ranks."""
+    from nanodiloco_b200.sync import PeerContext
+    gctx = PeerContext(world, rank, n, elem_bytes=4, device=dev, replicas=replicas, exchange="pull")
+    grad = gctx.local()[:n]
+    g = torch.Generator(device=dev).manual_seed(900 + rank)
+    m, v = torch.zeros(n, device=dev), torch.zeros(n, device=dev)
+    ss, sc = torch.zeros(1, device=dev), _lib.scratch(dev)
+    local = pctx.local()[:n]
+    grp = None
+    for k in range(world // replicas):                       # every rank creates every group
+        ranks = list(range(k * replicas, (k + 1) * replicas))
+        gk = dist.new_group(ranks)
+        if rank in ranks:
+            grp = gk
+
+    def fused(step):
+        gctx.inner_step_replicas(pctx, m, v, lr=4e-4, step=step, max_norm=1.0, sumsq_total_out=ss)
+
+    def plain(step):
+        dist.all_reduce(grad, op=dist.ReduceOp.AVG, group=grp)
+        _lib.sumsq(grad, ss, sc)
+        _lib.adamw(local, grad, m, v, lr=4e-4, step=step, sumsq_dev=ss, max_norm=1.0, zero_grad=True)
+
+    out = {}
+    for name, fn in (("fused_peer_ms", fused), ("allreduce_then_flat_kernels_ms", plain)):
+        for i in range(3):
+            grad.normal_(0, 1e-3, generator=g)
+            fn(i + 1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tot = 0.0
+        for i in range(K):
+            grad.normal_(0, 1e-3, generator=g)               # what the backward pass leaves behind (not timed)
+            dist.barrier()
+            torch.cuda.synchronize()
+            a.record()
+            fn(i + 4)
+            b.record()
+            torch.cuda.synchronize()
+            tot += a.elapsed_time(b)
+        t = torch.tensor([tot / K], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out[name] = float(t)
+    R = replicas
+    out["nvlink_bytes_per_dir"] = 2 * 4.0 * n * (R - 1) / R          # phase 1: gradient reads; phase 2: parameter writes
+    out["hbm_bytes_local"] = (4 + 4 + 16 + 16) * n / R + 4.0 * n * (R - 1) / R + 4.0 * n * (R - 1) / R
+    out["nvlink_gbs_per_dir"] = out["nvlink_bytes_per_dir"] / (out["fused_peer_ms"] * 1e-3) / 1e9
+    out["what"] = ("per inner step and GPU: each replica averages and steps 1/R of the flat space; NVLink per direction = "
+                   "(R-1)/R x 4 B/elem of gradient reads served/received plus (R-1)/R x 4 B/elem of parameter writes, in two "
+                   "phases; both timings include their flag barriers / NCCL launch")
+    del grad, m, v
+    gctx.close()
+    return out
+
+
 def _tokens_per_s(torch, dist, dev, world, args):
     """tokens/s of the drop-in training loop (BASELINE configs[1] model size) on synthetic tokens."""
     tokens = None
@@ -937,6 +994,15 @@ def native_arm(args):
         except Exception as e:  # noqa: BLE001
             extras = {"error": repr(e)}
 
+    # ---- configs[4]: the inner step of a worker that spans several GPUs (gradient exchange every step) ----
+    replica_inner = None
+    if mode == "p2p" and args.replicas > 1 and not bf16 and not args.no_replica_inner:
+        try:
+            replica_inner = _replica_inner_ms(torch, dist, _lib, dev, pctx, n, world, rank, args.replicas, peak)
+        except Exception as e:  # noqa: BLE001
+            replica_inner = {"error": repr(e)}
+            torch.cuda.empty_cache()
+
     # ---- tokens/s: the drop-in training loop on synthetic tokens (BASELINE configs[1] model) -----
     tokens = None
     if not args.no_tokens:
@@ -974,6 +1040,7 @@ def native_arm(args):
             "config": workload_config(args, n_real, len(shapes), world),
             "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "parity_check": parity, "nvlink_measured": nvlink_measured, "nccl_timeline": nccl_timeline,
+            "replica_inner_step": replica_inner,
             "p2p_exchange": pctx_exchange,
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
@@ -1020,6 +1087,7 @@ def main():
     ap.add_argument("--no-extras", action="store_true", help="skip the inner-step and reference-GPU-path timings")
     ap.add_argument("--nccl-single-comm", action="store_true", help="--sync nccl: all-gathers share the reduce-scatters' communicator")
     ap.add_argument("--nccl-no-register", action="store_true", help="--sync nccl: plain torch memory instead of ncclMemAlloc + ncclCommRegister")
+    ap.add_argument("--no-replica-inner", action="store_true", help="--replicas: skip the inner-step measurement")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of one extra step")
     ap.add_argument("--parity-elems", type=int, default=1 << 24, help="elements per rank the parity check compares")
     ap.add_argument("--p2p-exchange", choices=["auto", "pull", "push"], default="auto",

@@ -39,6 +39,17 @@ cfg)
   run_bench bf16 29551 $FAST --sync p2p --dtype bf16 --no-e2e
   run_bench cfg2_150m_bf16 29552 $FAST --sync p2p --dtype bf16 --workload llama150m --no-e2e
   [ $N -ge 4 ] && run_bench cfg5_rep2 29553 $FAST --sync p2p --replicas 2 --no-e2e;;
+push)
+  run_bench push 29512 --steps 10 --warmup 3 --no-tokens --no-extras --no-e2e --sync p2p --p2p-exchange push;;
+nccl256)
+  run_bench nccl256 29532 $FAST --sync nccl --bucket-mb 256 --streams 3 --no-e2e;;
+hybrid65)
+  run_bench hybrid65 29543 $FAST --sync hybrid --nvls-fraction 0.65 --no-e2e;;
+default)
+  timeout 600 $TR --master-port 29571 bench.py --gpus $N --steps 20 --warmup 5 2> $OUT/bench_n${N}_default_$TAG.err | grep '^{' > $OUT/bench_n${N}_default_$TAG.json; cut -c1-300 $OUT/bench_n${N}_default_$TAG.json; echo
+  run_bench default_again 29573 $FAST --sync p2p;;
+ref3)
+  timeout 600 $TR --master-port 29572 bench.py --impl reference --gpus $N --steps 3 --warmup 1 2> $OUT/bench_n${N}_ref3_$TAG.err | grep '^{' > $OUT/bench_n${N}_ref3_$TAG.json; cut -c1-2000 $OUT/bench_n${N}_ref3_$TAG.json; tail -3 $OUT/bench_n${N}_ref3_$TAG.err;;
 micro)
   timeout 600 $TR --master-port 29561 tools/microbench.py > $OUT/microbench_n${N}_$TAG.log 2>&1; tail -30 $OUT/microbench_n${N}_$TAG.log;;
 full)
