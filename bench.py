@@ -405,7 +405,8 @@ def _tokens_per_s(torch, dist, dev, world, args):
     if world > 1:
         dist.all_reduce(tk, op=dist.ReduceOp.MIN)
     tokens = {"value": float(tk) * world, "unit": "tokens/s", "per_worker_min": float(tk),
-              "outer_sync_ms": st["outer_sync_ms"], "params": st["params"],
+              "outer_sync_ms": st["outer_sync_ms"], "avg_sync_ms": st.get("avg_sync_ms"),
+              "avg_sync_wait_ms_rank0": st.get("avg_sync_wait_ms"), "params": st["params"],
               "what": f"nanodiloco_b200.main.train_model, 150M-class Llama (h1024 i2688 a16 L12, fp32 like the "
                       f"reference), per-device batch 8 x seq 1024, H={H} inner steps per outer sync ({rounds} rounds, "
                       f"first excluded), synthetic tokens; fwd/bwd is stock HF Llama (out of scope)"}

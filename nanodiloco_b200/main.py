@@ -181,6 +181,9 @@ def train_model(
         "tokens_per_s_per_worker": toks / wall, "tokens_per_s": world_size * toks / wall,
         "inner_steps_run": n_inner, "outer_steps_run": n_outer, "wall_s": wall,
         "outer_sync_ms": sync_ms, "excluded_first_round": bool(steady),
+        # of which: waiting for the slowest worker to arrive at the sync (skew, not cost of the sync)
+        "avg_sync_wait_ms": (lambda w: None if w is None else w * 1e3)(getattr(diloco_model, "avg_sync_wait_time", None)),
+        "avg_sync_ms": diloco_model.avg_sync_time * 1e3,
         "params": sum(p.numel() for p in model.parameters()), "losses": losses,
         "final_loss": float(loss.detach()),
     }
