@@ -47,7 +47,12 @@ hybrid65)
   run_bench hybrid65 29543 $FAST --sync hybrid --nvls-fraction 0.65 --no-e2e;;
 default)
   timeout 600 $TR --master-port 29571 bench.py --gpus $N --steps 20 --warmup 5 2> $OUT/bench_n${N}_default_$TAG.err | grep '^{' > $OUT/bench_n${N}_default_$TAG.json; cut -c1-300 $OUT/bench_n${N}_default_$TAG.json; echo
-  run_bench default_again 29573 $FAST --sync p2p;;
+  python - <<PY
+import json
+d=json.load(open('$OUT/bench_n${N}_default_$TAG.json')); p=d.get('parity_check') or {}; e=d.get('e2e') or {}; t=d.get('tokens_per_s') or {}
+print('default ms=%.3f frac=%.3f parity=%s e2e=%s ceil=%s tokens=%s wait_ms=%s sync_ms=%s' % (d['value'], d['roofline']['frac'], p.get('ok'), e.get('value'), e.get('host_link_ceiling_ms'), t.get('value'), t.get('avg_sync_wait_ms_rank0'), t.get('avg_sync_ms')), t.get('error',''))
+PY
+  ;;
 ref3)
   timeout 600 $TR --master-port 29572 bench.py --impl reference --gpus $N --steps 3 --warmup 1 2> $OUT/bench_n${N}_ref3_$TAG.err | grep '^{' > $OUT/bench_n${N}_ref3_$TAG.json; cut -c1-2000 $OUT/bench_n${N}_ref3_$TAG.json; tail -3 $OUT/bench_n${N}_ref3_$TAG.err;;
 micro)
