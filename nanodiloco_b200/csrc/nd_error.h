@@ -2,9 +2,11 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "../../include/nanodiloco_b200.h"
 
@@ -35,6 +37,22 @@ inline int check_launch(const char* what) {
     }
     return ND_OK;
 }
+
+// NVTX ranges around the phases the library enqueues (K1 / exchange / K2 / AdamW ...), visible in nsys and
+// `ncu --nvtx`.  Off unless ND_NVTX=1: a push/pop pair per phase costs nothing next to a multi-GB pass, but a
+// library should not emit markers nobody asked for.  nvtx3 is header-only; without a tool attached a call is
+// one load and a branch.
+inline bool nvtx_enabled() {
+    static const bool on = [] { const char* e = getenv("ND_NVTX"); return e && e[0] == '1'; }();
+    return on;
+}
+struct NvtxRange {
+    bool on;
+    explicit NvtxRange(const char* name) : on(nvtx_enabled()) { if (on) nvtxRangePushA(name); }
+    ~NvtxRange() { if (on) nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
+};
 
 #define ND_CUDA(call)                                                                          \
     do {                                                                                       \

@@ -447,11 +447,13 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
     const int workers = W / c->replicas;
     if (push && (size_t)workers * shard_bytes > c->staging_bytes)
         return set_error(ND_EINVAL, "nd_outer_sync_p2p: the staging area holds fewer than workers*shard bytes");
+    NvtxRange range_all(push ? "nd_outer_sync_p2p (push)" : "nd_outer_sync_p2p (pull)");
     ND_CUDA(cudaEventRecord(c->t0, stream));
     int rc;
     void *reads[ND_MAX_WORKERS], *writes[ND_MAX_WORKERS];
     fill_rw(c, (size_t)c->rank * shard_bytes, reads, writes);
     if (push) {
+        NvtxRange range("nd.p2p: push slices to the shard owners");
         // phase A: the first replica of every worker writes its copy of shard r into slot [worker] of rank r
         if (c->rank % c->replicas == 0 && shard_bytes > 0) {
             PushArgs a;
@@ -477,8 +479,11 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
     // also means its inner steps are done and it has finished reading its own copy)
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;
     ND_CUDA(cudaEventRecord(c->tb, stream));
-    rc = nd_outer_fused_rw(master_shard, mom_shard, reads, workers, writes, W, local_dtype, shard, lr, mu, dampening,
-                           wd, nesterov, first_step, sumsq_out, scratch, stream_);
+    {
+        NvtxRange range("nd.p2p: fused average + Nesterov update + copy-back");
+        rc = nd_outer_fused_rw(master_shard, mom_shard, reads, workers, writes, W, local_dtype, shard, lr, mu, dampening,
+                               wd, nesterov, first_step, sumsq_out, scratch, stream_);
+    }
     if (rc) return rc;
     if (W > 1 && (rc = nd_peer_barrier(c, stream_))) return rc;  // every shard of our copy has been written
     ND_CUDA(cudaEventRecord(c->t1, stream));
@@ -748,6 +753,7 @@ int nd_inner_step_replicas(nd_peer_ctx* pc, nd_peer_ctx* gc, float* m, float* v,
     char* mine_g = static_cast<char*>(gc->base[gc->rank]);
     float* my_part = reinterpret_cast<float*>(mine_g + gc->bytes + kPartialOffset);
     int rc;
+    NvtxRange range_all("nd_inner_step_replicas");
     // every replica's backward pass has finished writing its gradient buffer
     if (R > 1 && (rc = peer_barrier_group(gc, 4, first, R, stream))) return rc;
     if ((rc = nd_grad_avg(grads, R, mine_g + off, dtype, part, my_part, gc->scratch, stream_))) return rc;

@@ -264,6 +264,7 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
         return set_error(ND_EINVAL, "nd_outer_sync: null pointer");
     cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
     const int W = c->world;
+    NvtxRange range_all("nd_outer_sync (NCCL pipeline)");
 
     ND_CUDA(cudaEventRecord(c->t0, stream));
     if (W == 1) {
@@ -309,6 +310,7 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
         cudaStream_t s = c->streams[b % c->n_streams];
         float* pb = pg + off;
         int rc;
+        NvtxRange range("nd.sync.bucket: K1 pseudo-gradient + reduce-scatter");
         if ((rc = mark(b, 0, s))) return rc;
         rc = nd_pseudo_grad(master + off, local + off, ND_F32, pb, len, reinterpret_cast<nd_stream_t>(s));
         if (rc) return rc;
@@ -325,6 +327,7 @@ int nd_outer_sync(nd_sync_ctx* c, float* local, float* master, float* mom_shard,
         const int64_t shard_off = b * (c->bucket / W);
         cudaStream_t s = c->streams[b % c->n_streams];
         int rc;
+        NvtxRange range("nd.sync.bucket: K2 shard update + all-gather + master refresh");
         if ((rc = mark(b, 3, s))) return rc;
         rc = nd_outer_nesterov(master + mine, mom_shard + shard_off, pg + mine, local + mine, ND_F32, slice,
                                (float)W, lr, mu, dampening, wd, nesterov, first_step, nullptr, nullptr,

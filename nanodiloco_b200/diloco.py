@@ -384,6 +384,8 @@ class Diloco:
         stream = torch.cuda.current_stream(self.device)
         t0 = torch.cuda.Event(enable_timing=True)
         t1 = torch.cuda.Event(enable_timing=True)
+        if self._fold_wait:          # the previous sync finished long ago: take its wait share before it is overwritten
+            self._fold_wait_now()
         _nvtx_push("nd.outer_step[%s]" % self.sync_mode)
         t0.record(stream)
         first = self._first_outer
@@ -719,16 +721,63 @@ class Diloco:
     def _fold_timings(self) -> None:
         for t0, t1 in self._pending_events:
             t1.synchronize()
-            self._sync_time += t0.elapsed_time(t1) / 1e3
+            self._last_total_ms = t0.elapsed_time(t1)
+            self._sync_time += self._last_total_ms / 1e3
             self._sync_calls += 1
         self._pending_events.clear()
         if getattr(self, "_fold_wait", False):
-            # the peer context brackets the flag barrier that absorbs the skew between workers; only the
-            # LAST sync's split is kept by the library, so this is a running mean over the syncs observed
-            _, wait_ms = self._peer.last_ms2()
-            self._wait_time += wait_ms / 1e3
-            self._wait_calls += 1
-            self._fold_wait = False
+            self._fold_wait_now()
+
+    def _fold_wait_now(self) -> None:
+        # the peer context brackets the flag barrier that absorbs the skew between workers; the library keeps
+        # the LAST sync's split, so it is collected before the next sync starts and whenever a timing is read
+        tot_ms, wait_ms = self._peer.last_ms2()
+        self._wait_time += wait_ms / 1e3
+        self._wait_calls += 1
+        self._last_sync = {"total_ms": tot_ms, "wait_ms": wait_ms, "work_ms": tot_ms - wait_ms}
+        self._fold_wait = False
+
+    def sync_counters(self) -> dict:
+        """Counters of the LAST outer sync (waits for it to finish).  Always: device `ms`, and where the sync
+        moves data between GPUs `nvlink_gb_per_dir` (algorithmic: reduce-scatter + all-gather bytes of the
+        working copy per GPU and direction) and `nvlink_gbs_per_dir`.  Peer-memory sync: `wait_ms` (first flag
+        barrier: skew between workers) and `work_ms`, the bandwidth being taken over the work.  NCCL pipeline
+        with `profile_buckets(True)`: `buckets`, one row per bucket with the stage times and the bus GB/s of its
+        reduce-scatter and all-gather."""
+        self._fold_timings()
+        W, n = self.world_size, self.layout.total
+        esz = 2 if self.working_dtype == torch.bfloat16 else 4
+        out = {"sync": self.sync_mode, "elements": n}
+        wire = 2.0 * esz * n * (W - 1) / W if W > 1 else 0.0
+        if self._peer is not None and not self.offload_master and getattr(self, "_last_sync", None):
+            out.update(self._last_sync)
+            ms = self._last_sync["work_ms"]
+        elif self._peer is not None or self._nvls is not None:
+            ms = (self._peer or self._nvls).last_ms()
+        elif self._ctx is not None:
+            ms = self._ctx.last_ms()
+            rows = self._ctx.timeline()
+            if rows:
+                blen = min(self._ctx.bucket, n)
+                per = 4.0 * blen * (W - 1) / W
+                for r in rows:
+                    r["rs_bus_gbs"] = per / max(1e-9, (r["rs"][1] - r["rs"][0]) * 1e-3) / 1e9
+                    r["ag_bus_gbs"] = per / max(1e-9, (r["ag"][1] - r["ag"][0]) * 1e-3) / 1e9
+                out["buckets"] = rows
+        else:
+            ms = self._last_total_ms if hasattr(self, "_last_total_ms") else self.avg_sync_time * 1e3
+        out["ms"] = ms
+        if wire:
+            out["nvlink_gb_per_dir"] = wire / 1e9
+            out["nvlink_gbs_per_dir"] = wire / max(1e-9, ms * 1e-3) / 1e9
+        else:
+            out["hbm_gbs"] = (16.0 + 2 * esz) * n / max(1e-9, ms * 1e-3) / 1e9
+        return out
+
+    def profile_buckets(self, on: bool = True) -> None:
+        """NCCL pipeline: record the per-bucket stage events that `sync_counters()['buckets']` reports."""
+        if self._ctx is not None:
+            self._ctx.set_profiling(on)
 
     @property
     def avg_sync_wait_time(self):

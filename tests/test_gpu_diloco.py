@@ -54,6 +54,9 @@ def test_outer_step_drop_in_w1(golden_dir):
         assert np.array_equal(host(_flat(d.offloaded_last_sync_parameters)), z[f"params_r{r}"])
     assert ptrs == [p.data_ptr() for p in params] and ids == [id(p) for p in params]   # storage never moves
     assert d.avg_sync_time > 0                                        # diloco.py:62-64, now real
+    c = d.sync_counters()                                             # counters of the last sync
+    assert c["sync"] == "none" and c["ms"] > 0 and c["hbm_gbs"] > 0 and d.avg_sync_wait_time is None
+    assert float(d.last_outer_grad_norm) > 0
     sd = outer.state_dict()
     assert len(sd["state"]) == len(params)
 

@@ -127,6 +127,10 @@ def _golden_case(mode, bucket_mb, world, rank):
     if mode in ("p2p", "p2p_push"):
         w = d.avg_sync_wait_time
         ok &= chk("avg_sync_wait_time is a non-negative number", w is not None and w >= 0.0)
+    c = d.sync_counters()
+    ok &= chk("sync_counters: ms and NVLink GB/s of the last sync", c["ms"] > 0 and c["nvlink_gbs_per_dir"] > 0)
+    if mode in ("p2p", "p2p_push"):
+        ok &= chk("sync_counters: wait + work = total", abs(c["wait_ms"] + c["work_ms"] - c["total_ms"]) < 1e-3)
     sd = d.state_dict()                       # collective: full master and momentum on every rank
     saved = torch.cat([v.reshape(-1) for v in d.layout.views(sd["master"])]).numpy()
     ok &= chk("np.array_equal(widen(saved), f32(params))", np.array_equal(widen(saved), f32(params)))                 # just synced: theta_sync == params
