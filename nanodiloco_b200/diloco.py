@@ -572,6 +572,8 @@ class Diloco:
             dst.copy_(src)
         self._first_outer = bool(sd["first_outer"])
         self._inner_step_count = int(sd["inner_step_count"])
+        if self.fused_inner:
+            self._step_tensor.fill_(float(self._inner_step_count))
         self.scheduler.load_state_dict(sd["scheduler"])
         self._publish_outer_state()
 

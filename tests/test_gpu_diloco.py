@@ -235,6 +235,60 @@ def test_state_dict_round_trip(golden_dir):
         assert np.array_equal(host(mom), z[f"mom_r{r}"])
 
 
+def test_stock_optimizer_state_dicts_round_trip(golden_dir):
+    """A checkpoint layer written against the reference saves `inner_optimizer.state_dict()` and
+    `outer_optimizer.state_dict()` (plus the model) and loads them back.  torch's load_state_dict replaces the
+    state tensors -- which here are views of the flat buffers -- by fresh ones; the wrapper's hooks copy them
+    back, so a resumed run continues with the same bits as the uninterrupted one."""
+    z = np.load(os.path.join(golden_dir, "inner.npz"))
+    zo = np.load(os.path.join(golden_dir, "outer_w1.npz"))
+
+    def grads(params, s):
+        off = 0
+        for p in params:
+            p.grad = torch.from_numpy(z[f"grad_s{s}"][off:off + p.numel()].copy()).reshape(p.shape).cuda()
+            off += p.numel()
+
+    def drift(params, r):
+        off = 0
+        with torch.no_grad():
+            for p in params:
+                p.add_(torch.from_numpy(zo[f"local_r{r}_w0"][off:off + p.numel()] * 0.01).reshape(p.shape).cuda())
+                off += p.numel()
+
+    def run(d, model, first_step, steps):
+        for s in range(first_step, first_step + steps):
+            grads(list(model.parameters()), s)
+            d.inner_step()
+        drift(list(model.parameters()), 1)
+        d.outer_step()
+
+    model, inner, outer, d = _make(z, warmup_steps=2, total_steps=10)
+    run(d, model, 0, 3)
+    import copy
+    # state_dict() hands out references (as in stock torch); a checkpoint is a copy of them
+    ckpt = copy.deepcopy({"model": model.state_dict(), "inner": inner.state_dict(), "outer": outer.state_dict(),
+                          "diloco": d.state_dict()})
+    assert len(ckpt["outer"]["state"]) == len(list(model.parameters()))
+    run(d, model, 3, 3)                                                   # the uninterrupted run goes on
+    want = _flat(model.parameters()).clone()
+    want_m = _flat([inner.state[p]["exp_avg"] for p in model.parameters()]).clone()
+    want_b = _flat([outer.state[p]["momentum_buffer"] for p in model.parameters()]).clone()
+
+    model2, inner2, outer2, d2 = _make(z, warmup_steps=2, total_steps=10)
+    ptrs = [p.data_ptr() for p in model2.parameters()]
+    model2.load_state_dict(ckpt["model"])
+    inner2.load_state_dict(ckpt["inner"])
+    outer2.load_state_dict(ckpt["outer"])
+    d2.load_state_dict(ckpt["diloco"])                                    # theta_sync, scheduler, step counters
+    assert ptrs == [p.data_ptr() for p in model2.parameters()]            # still living in the flat buffer
+    assert float(inner2.state[next(iter(model2.parameters()))]["step"]) == 3
+    run(d2, model2, 3, 3)
+    assert torch.equal(_flat(model2.parameters()), want)
+    assert torch.equal(_flat([inner2.state[p]["exp_avg"] for p in model2.parameters()]), want_m)
+    assert torch.equal(_flat([outer2.state[p]["momentum_buffer"] for p in model2.parameters()]), want_b)
+
+
 def test_frozen_parameters_are_left_alone_by_the_inner_step():
     """torch's AdamW skips parameters without a gradient: a frozen tensor must not even be weight-decayed."""
     torch.manual_seed(0)
