@@ -777,6 +777,9 @@ def native_arm(args):
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "kernel": kern_name, "peak_source": peak_src,
+                "traffic_source": ("dram__bytes_read.sum + dram__bytes_write.sum of ONE `ncu --set full` capture of this "
+                                   "kernel on the 150M-class space (profiles/traffic.json, 214,983,680 elements), scaled "
+                                   "by element count to this launch -- not measured in this run") if traffic else None,
                 "algorithmic_bytes_per_launch": kern_bytes, "kernel_ms": kern_ms}
 
     # ---- whole-step roofline (HBM and NVLink), for the record ---------------------------------
