@@ -660,7 +660,8 @@ def native_arm(args):
     if mode == "p2p":
         # one fused kernel per GPU over NVLink peer memory; master and momentum sharded 1/W
         pctx = PeerContext(world, rank, n, elem_bytes=2 if bf16 else 4, group=None, device=dev,
-                           replicas=args.replicas, exchange=args.p2p_exchange)
+                           replicas=args.replicas, exchange=args.p2p_exchange,
+                           fold=False if args.p2p_no_fold else None)
         pctx_exchange = pctx.exchange
         local = pctx.local(wdtype)[:n]
         # replicas of one worker hold identical parameters: seed the drift per worker, not per rank
@@ -1031,7 +1032,9 @@ def native_arm(args):
     if mode in ("nvls", "hybrid"):
         launches_per_step = 4                                          # K1, barrier, NVLS kernel, barrier
     elif mode == "p2p":
-        launches_per_step = 3                                          # barrier, fused kernel, barrier
+        folded = pctx_exchange == "pull" and not args.p2p_no_fold and os.environ.get("ND_P2P_FOLD", "1") != "0"
+        # pull: ONE launch (rendezvous folded into the fused kernel) or barrier, kernel, barrier; push adds the copy kernel
+        launches_per_step = 1 if folded else (4 if pctx_exchange == "push" else 3)
     elif world > 1:
         launches_per_step = 2 * ((n + ctx.bucket - 1) // ctx.bucket)   # K1 + K2 per bucket
     else:
@@ -1045,7 +1048,7 @@ def native_arm(args):
             "roofline": roofline, "step_roofline": step_roof, "cpu_baseline": cpu_baseline, "e2e": e2e,
             "parity_check": parity, "nvlink_measured": nvlink_measured, "nccl_timeline": nccl_timeline,
             "replica_inner_step": replica_inner,
-            "p2p_exchange": pctx_exchange,
+            "p2p_exchange": pctx_exchange, "launches_per_step": launches_per_step,
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": int(launches_per_step * K),
             "params_per_worker": n_real, "worker_params_per_s": world * n_real / (ms * 1e-3),
@@ -1094,6 +1097,8 @@ def main():
     ap.add_argument("--no-replica-inner", action="store_true", help="--replicas: skip the inner-step measurement")
     ap.add_argument("--no-parity", action="store_true", help="skip the oracle check of one extra step")
     ap.add_argument("--parity-elems", type=int, default=1 << 24, help="elements per rank the parity check compares")
+    ap.add_argument("--p2p-no-fold", action="store_true",
+                    help="--sync p2p: barrier launches around the fused kernel instead of rendezvous folded into it")
     ap.add_argument("--p2p-exchange", choices=["auto", "pull", "push"], default="auto",
                     help="--sync p2p: how the worker copies reach the shard owner (nd_peer_set_mode)")
     args = ap.parse_args()

@@ -431,6 +431,13 @@ int nd_inner_step_replicas(nd_peer_ctx* params_ctx, nd_peer_ctx* grads_ctx, floa
                            double weight_decay, int64_t step, float max_norm, float* sumsq_total_out,
                            nd_stream_t stream);
 
+/* nd_outer_sync_p2p (pull) normally runs as ONE launch per GPU: the arrival rendezvous of the ranks sits in
+ * the fused kernel's prologue (no block reads a peer's copy before every worker has published its arrival) and
+ * the completion rendezvous in its epilogue (the block that finishes last publishes and awaits the "done"
+ * flags).  on = 0 brackets the kernel with two barrier launches instead (ND_P2P_FOLD=0 does the same); the
+ * results are the same bits.  Calls on all ranks must agree. */
+int nd_peer_set_fold(nd_peer_ctx* ctx, int on);
+
 /* nd_peer_last_ms plus the part of it spent in the first flag barrier of nd_outer_sync_p2p, i.e.
  * waiting for the slowest worker to arrive (the skew the reference's blocking all_reduce, diloco.py:49,
  * hides inside the collective).  work = total - wait. */

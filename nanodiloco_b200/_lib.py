@@ -87,6 +87,7 @@ SIGNATURES = {
     "nd_peer_last_ms": (_c_i, [_c_p, ctypes.POINTER(_c_f)]),
     "nd_peer_set_staging": (_c_i, [_c_p, ctypes.c_size_t, ctypes.c_size_t]),
     "nd_peer_set_mode": (_c_i, [_c_p, _c_i]),
+    "nd_peer_set_fold": (_c_i, [_c_p, _c_i]),
     "nd_peer_last_ms2": (_c_i, [_c_p, ctypes.POINTER(_c_f), ctypes.POINTER(_c_f)]),
 }
 

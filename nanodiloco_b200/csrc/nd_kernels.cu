@@ -666,10 +666,11 @@ static int launch_table(const Op& op, const nd_tensor_desc* tab, int T, int64_t 
 
 
 // TMA-staged launch: TILE fp32 slots per buffer, STAGES stages, THREADS threads, MINB CTAs per SM.
-template <int TILE, int STAGES, int THREADS, int MINB, class TileOp>
-static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_out, cudaStream_t s) {
-    if (n == 0 && !TileOp::kHasSum) return ND_OK;
-    auto kernel = tma::tile_kernel<TILE, STAGES, THREADS, MINB, TileOp>;
+template <int TILE, int STAGES, int THREADS, int MINB, class TileOp, bool PEER = false>
+static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_out, cudaStream_t s,
+                       const tma::PeerSync* peer = nullptr) {
+    if (n == 0 && !TileOp::kHasSum && !PEER) return ND_OK;   // a rendezvous is kept even when there is no data
+    auto kernel = tma::tile_kernel<TILE, STAGES, THREADS, MINB, TileOp, PEER>;
     constexpr size_t smem = (size_t)STAGES * TileOp::kBufs * TILE * sizeof(float);
     static_assert(smem <= 227 * 1024, "stage set exceeds the 227 KB of shared memory a CTA can have");
     static std::atomic<bool> configured[64];   // per device; two threads racing here both set the same attribute
@@ -684,7 +685,8 @@ static int launch_tile(const TileOp& op, int64_t n, void* scratch, float* sum_ou
     int64_t full = (int64_t)sm_count() * MINB;
     int64_t g = ntiles < full ? (ntiles > 0 ? ntiles : 1) : full;
     if (g > kMaxPartials) g = kMaxPartials;
-    kernel<<<(int)g, THREADS, smem, s>>>(op, n, static_cast<Scratch*>(scratch), sum_out);
+    kernel<<<(int)g, THREADS, smem, s>>>(op, n, static_cast<Scratch*>(scratch), sum_out,
+                                         peer ? *peer : tma::PeerSync{});
     return check_launch("tile_kernel");
 }
 
@@ -758,7 +760,8 @@ constexpr int U_ADAM = 1, B_ADAM = 2;
 
 template <int W, bool BF16, bool SUM>
 static int launch_fused(float* master, float* mom, void* const* locals, int w_rt, void* const* writes, int n_writes,
-                        int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s) {
+                        int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s,
+                        const tma::PeerSync* peer = nullptr, bool* peer_done = nullptr) {
     OuterFusedOp<W, BF16, SUM> op;
     op.master = master; op.mom = mom; op.w_rt = w_rt; op.world = (float)w_rt; op.h = h; op.acc = 0.f;
     op.n_writes = n_writes;
@@ -769,6 +772,14 @@ static int launch_fused(float* master, float* mom, void* const* locals, int w_rt
         al = al && aligned16(op.locals.p[k]) && aligned16(op.writes.p[k]);
     }
     if constexpr (W > 0) {
+        if (al && peer) {   // the same kernels with the two cross-GPU rendezvous folded in (nd_outer_sync_p2p)
+            FusedTileOp<W, BF16, SUM> t{op};
+            *peer_done = true;
+            if constexpr (W == 1) return launch_tile<ND_TILE_FUSED1, FusedTileOp<W, BF16, SUM>, true>(t, n, scratch, sumsq_out, s, peer);
+            else if constexpr (W == 2) return launch_tile<ND_TILE_FUSED2, FusedTileOp<W, BF16, SUM>, true>(t, n, scratch, sumsq_out, s, peer);
+            else if constexpr (W <= 4) return launch_tile<ND_TILE_FUSED4, FusedTileOp<W, BF16, SUM>, true>(t, n, scratch, sumsq_out, s, peer);
+            else return launch_tile<ND_TILE_FUSED8, FusedTileOp<W, BF16, SUM>, true>(t, n, scratch, sumsq_out, s, peer);
+        }
         if (al) {  // TMA-staged path: every bulk copy needs 16-byte aligned addresses
             FusedTileOp<W, BF16, SUM> t{op};
             if constexpr (W == 1) return launch_tile<ND_TILE_FUSED1>(t, n, scratch, sumsq_out, s);
@@ -786,19 +797,39 @@ static int launch_fused(float* master, float* mom, void* const* locals, int w_rt
         }
     }
     // register-staged path: unaligned buffers (scalar accesses) and run-time worker counts
+    if (peer) return ND_OK;   // not launched: *peer_done stays false and the caller uses separate barrier launches
     return launch_flat<1, 2>(op, n, scratch, sumsq_out, s);
 }
 
 template <bool BF16, bool SUM>
 static int dispatch_fused(int W, float* master, float* mom, void* const* locals, void* const* writes, int n_writes,
-                          int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s) {
+                          int64_t n, const OuterHyper& h, float* sumsq_out, void* scratch, cudaStream_t s,
+                          const tma::PeerSync* peer = nullptr, bool* peer_done = nullptr) {
 #define ND_CASE(w) \
-    case w: return launch_fused<w, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s)
+    case w: return launch_fused<w, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s, \
+                                              peer, peer_done)
     switch (W) {
         ND_CASE(1); ND_CASE(2); ND_CASE(3); ND_CASE(4); ND_CASE(8);
-        default: return launch_fused<0, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s);
+        default: return launch_fused<0, BF16, SUM>(master, mom, locals, W, writes, n_writes, n, h, sumsq_out, scratch, s,
+                                                   peer, peer_done);
     }
 #undef ND_CASE
+}
+
+// nd_outer_fused_rw with the two cross-GPU rendezvous of nd_outer_sync_p2p folded into the kernel (internal to the
+// library: nd_peer.cu).  *launched = false when the buffers do not qualify for the TMA-staged kernel; nothing was
+// enqueued then and the caller falls back to barrier launches around nd_outer_fused_rw.
+int outer_fused_rw_peer(float* master, float* mom, void* const* reads, int W, void* const* writes, int n_writes,
+                        int local_dtype, int64_t n, float lr, float mu, float dampening, float wd, int nesterov,
+                        int first_step, float* sumsq_out, void* scratch, cudaStream_t s, const tma::PeerSync& peer,
+                        bool* launched) {
+    *launched = false;
+    OuterHyper h = make_outer_hyper(lr, mu, dampening, wd, nesterov, first_step);
+    if (local_dtype == ND_BF16)
+        return sumsq_out ? dispatch_fused<true, true>(W, master, mom, reads, writes, n_writes, n, h, sumsq_out, scratch, s, &peer, launched)
+                         : dispatch_fused<true, false>(W, master, mom, reads, writes, n_writes, n, h, nullptr, nullptr, s, &peer, launched);
+    return sumsq_out ? dispatch_fused<false, true>(W, master, mom, reads, writes, n_writes, n, h, sumsq_out, scratch, s, &peer, launched)
+                     : dispatch_fused<false, false>(W, master, mom, reads, writes, n_writes, n, h, nullptr, nullptr, s, &peer, launched);
 }
 
 }  // namespace nd

@@ -25,6 +25,12 @@
 
 namespace nd {
 
+// nd_kernels.cu: the fused outer kernel with the two cross-GPU rendezvous folded in
+int outer_fused_rw_peer(float* master, float* mom, void* const* reads, int W, void* const* writes, int n_writes,
+                        int local_dtype, int64_t n, float lr, float mu, float dampening, float wd, int nesterov,
+                        int first_step, float* sumsq_out, void* scratch, cudaStream_t s, const tma::PeerSync& peer,
+                        bool* launched);
+
 constexpr size_t kFlagBytes = 4096;  // per-rank flag page appended to the shared buffer
 
 __device__ __forceinline__ unsigned long long global_ns() {
@@ -186,6 +192,12 @@ struct nd_peer_ctx {
     uint32_t** flag_pages_dev = nullptr;
     static constexpr int kChannels = 6;   // 0 outer sync, 1-3 in-switch pipeline lanes, 4 replicas of one worker
     uint32_t epoch[kChannels] = {0, 0, 0, 0, 0, 0};
+    // nd_outer_sync_p2p with the rendezvous folded into the fused kernel: a block counter, the time block 0 waited
+    // for the slowest worker, and whether the last sync ran that way
+    unsigned* done_dev = nullptr;
+    unsigned long long* wait_ns_dev = nullptr;
+    int fold = 1;                         // ND_P2P_FOLD=0 / nd_peer_set_fold(ctx, 0): barrier kernels around the fused kernel
+    bool last_folded = false;
     void* scratch = nullptr;              // norm scratch of nd_inner_step_replicas (nd_scratch_bytes), created on first use
     int replicas = 1;                 // consecutive ranks that hold identical copies of one worker
     size_t staging_off = 0, staging_bytes = 0;   // push mode: where in every rank's buffer the staging slots start
@@ -223,6 +235,10 @@ static int peer_ctx_finish(nd_peer_ctx* c) {
     memset(c->diag_host, 0, 4 * sizeof(int));
     ND_CUDA(cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->diag_dev), c->diag_host, 0));
     c->timeout_ns = peer_timeout_ns();
+    ND_CUDA(cudaMalloc(&c->done_dev, 16));
+    ND_CUDA(cudaMemset(c->done_dev, 0, 16));
+    c->wait_ns_dev = reinterpret_cast<unsigned long long*>(c->done_dev) + 1;
+    if (const char* e = getenv("ND_P2P_FOLD")) c->fold = atoi(e) != 0;
     ND_CUDA(cudaEventCreate(&c->t0));
     ND_CUDA(cudaEventCreate(&c->t1));
     ND_CUDA(cudaEventCreate(&c->ta));
@@ -333,6 +349,7 @@ int nd_peer_ctx_destroy(nd_peer_ctx* c) {
     if (c->flag_pages_dev) cudaFree(c->flag_pages_dev);
     if (c->diag_host) cudaFreeHost(c->diag_host);
     if (c->scratch) cudaFree(c->scratch);
+    if (c->done_dev) cudaFree(c->done_dev);
     if (c->t0) cudaEventDestroy(c->t0);
     if (c->t1) cudaEventDestroy(c->t1);
     if (c->ta) cudaEventDestroy(c->ta);
@@ -387,6 +404,12 @@ int nd_peer_set_staging(nd_peer_ctx* c, size_t byte_offset, size_t bytes) {
                                     "the peer buffer");
     c->staging_off = byte_offset;
     c->staging_bytes = bytes;
+    return ND_OK;
+}
+
+int nd_peer_set_fold(nd_peer_ctx* c, int on) {
+    if (!c) return set_error(ND_ESTATE, "nd_peer_set_fold: null context");
+    c->fold = on != 0;
     return ND_OK;
 }
 
@@ -474,6 +497,28 @@ int nd_outer_sync_p2p(nd_peer_ctx* c, float* master_shard, float* mom_shard, int
             if (k * c->replicas != c->rank)
                 reads[k] = static_cast<char*>(c->base[c->rank]) + c->staging_off + (size_t)k * shard_bytes;
     }
+    if (W > 1 && c->fold && !push) {
+        // ONE launch: arrival rendezvous in the kernel's prologue, completion rendezvous in its epilogue
+        tma::PeerSync ps;
+        ps.flag_pages = c->flag_pages_dev; ps.first = 0; ps.count = W; ps.rank = c->rank;
+        ps.ch_in = 0; ps.ch_out = 5;
+        ps.epoch_in = c->epoch[0] + 1; ps.epoch_out = c->epoch[5] + 1;
+        ps.timeout_ns = c->timeout_ns; ps.diag = c->diag_dev; ps.done = c->done_dev; ps.wait_ns = c->wait_ns_dev;
+        bool launched = false;
+        NvtxRange range("nd.p2p: rendezvous + fused average + Nesterov update + copy-back + rendezvous");
+        rc = outer_fused_rw_peer(master_shard, mom_shard, reads, workers, writes, W, local_dtype, shard, lr, mu,
+                                 dampening, wd, nesterov, first_step, sumsq_out, scratch, stream, ps, &launched);
+        if (rc) return rc;
+        if (launched) {
+            c->epoch[0] += 1; c->epoch[5] += 1;
+            ND_CUDA(cudaEventRecord(c->t1, stream));
+            c->timed = true;
+            c->split = false;
+            c->last_folded = true;
+            return ND_OK;
+        }
+    }
+    c->last_folded = false;
     ND_CUDA(cudaEventRecord(c->ta, stream));
     // pull: every worker's inner steps are done.  push: every worker's slices have landed here (which
     // also means its inner steps are done and it has finished reading its own copy)
@@ -782,6 +827,11 @@ int nd_peer_last_ms2(nd_peer_ctx* c, float* total_ms_out, float* wait_ms_out) {
     *wait_ms_out = 0.0f;
     // only nd_outer_sync_p2p brackets its first barrier; the other variants report wait = 0
     if (c->split) ND_CUDA(cudaEventElapsedTime(wait_ms_out, c->ta, c->tb));
+    if (c->last_folded) {   // the kernel's block 0 timed its own arrival wait
+        unsigned long long ns = 0;
+        ND_CUDA(cudaMemcpy(&ns, c->wait_ns_dev, sizeof(ns), cudaMemcpyDeviceToHost));
+        *wait_ms_out = (float)((double)ns * 1e-6);
+    }
     return ND_OK;
 }
 

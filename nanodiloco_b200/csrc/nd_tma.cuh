@@ -88,6 +88,66 @@ __device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bu
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// ---- flag barriers across GPUs folded into a tile kernel ------------------------------------------------
+// The peer-memory outer sync needs two rendezvous of the ranks: before the kernel reads the peers' copies
+// (every worker has finished its inner steps) and after it has written them (every shard of every copy is
+// complete).  As kernels of their own they cost two launches and two drains of the GPU per sync, which is most
+// of the step for small models.  Folded: block 0 publishes this rank's arrival to every peer's flag page and
+// EVERY block polls the local page before its first load; after the last bulk store has completed, the block
+// that finishes last publishes "done" and alone waits for the peers' "done" flags, so that the end of the
+// kernel still means "my copy is complete".  Flags are monotonically increasing epochs in peer memory
+// (system-scope release/acquire), one slot per (channel, sender).  A wait is bounded by wall time
+// (`timeout_ns`, 0 = none): on expiry the rank records whom it waited for in `diag` (host-mapped) and traps.
+struct PeerSync {
+    uint32_t* const* flag_pages;   // device array: flag page of every rank (peer-mapped)
+    int first, count, rank;        // the ranks [first, first + count) meet
+    uint32_t epoch_in, epoch_out;  // value this sync publishes / awaits on the two channels
+    int ch_in, ch_out;
+    unsigned long long timeout_ns;
+    int* diag;                     // {timed_out, waited_for_rank, channel, epoch}
+    unsigned* done;                // device counter of finished blocks, zero at rest
+    unsigned long long* wait_ns;   // out: nanoseconds block 0 spent waiting for the slowest rank to arrive
+};
+
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// thread t < count of the calling block: tell rank first+t that this rank has reached `epoch` on `channel`
+__device__ __forceinline__ void peer_publish(const PeerSync& ps, int channel, uint32_t epoch) {
+    if ((int)threadIdx.x < ps.count) {
+        __threadfence_system();
+        uint32_t* remote = ps.flag_pages[ps.first + threadIdx.x] + channel * ND_MAX_WORKERS + ps.rank;
+        asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(remote), "r"(epoch) : "memory");
+    }
+}
+
+// thread t < count of the calling block: wait until rank first+t has reached `epoch` on `channel`
+__device__ __forceinline__ void peer_await(const PeerSync& ps, int channel, uint32_t epoch) {
+    if ((int)threadIdx.x < ps.count) {
+        const int w = ps.first + threadIdx.x;
+        const uint32_t* mine = ps.flag_pages[ps.rank] + channel * ND_MAX_WORKERS + w;
+        const unsigned long long t0 = global_ns();
+        for (unsigned spins = 0;; ++spins) {
+            uint32_t v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(mine) : "memory");
+            if ((int32_t)(v - epoch) >= 0) break;
+            if (ps.timeout_ns && (spins & 1023u) == 1023u && global_ns() - t0 > ps.timeout_ns) {
+                if (ps.diag) {
+                    ps.diag[1] = w; ps.diag[2] = channel; ps.diag[3] = (int)epoch;
+                    __threadfence_system();
+                    ps.diag[0] = 1;
+                }
+                __threadfence_system();
+                __trap();
+            }
+        }
+        __threadfence_system();
+    }
+}
+
 // One stage of shared memory: kBufs buffers of TILE fp32 slots each.
 template <int TILE>
 struct Stage {
@@ -95,8 +155,10 @@ struct Stage {
     __device__ __forceinline__ float* buf(int k) const { return base + (size_t)k * TILE; }
 };
 
-template <int TILE, int STAGES, int THREADS, int MINB, class TileOp>
-__global__ void __launch_bounds__(THREADS, MINB) tile_kernel(TileOp op, int64_t n, Scratch* sc, float* sum_out) {
+template <int TILE, int STAGES, int THREADS, int MINB, class TileOp, bool PEER = false>
+__global__ void __launch_bounds__(THREADS, MINB) tile_kernel(TileOp op, int64_t n, Scratch* sc, float* sum_out,
+                                                             PeerSync ps) {
+    static_assert(!PEER || THREADS >= ND_MAX_WORKERS, "one polling thread per rank");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float* sm = reinterpret_cast<float*>(smem_raw);
     __shared__ uint64_t full[STAGES];
@@ -109,6 +171,17 @@ __global__ void __launch_bounds__(THREADS, MINB) tile_kernel(TileOp op, int64_t 
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) mbar_init(&full[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if constexpr (PEER) {
+        // arrival rendezvous: nothing of the peers' copies is read before every worker has published its arrival
+        unsigned long long t0 = 0;
+        if (blockIdx.x == 0) {
+            peer_publish(ps, ps.ch_in, ps.epoch_in);
+            if (tid == 0) t0 = global_ns();
+        }
+        peer_await(ps, ps.ch_in, ps.epoch_in);
+        asm volatile("fence.proxy.async;" ::: "memory");   // the bulk-copy engine reads what the acquire made visible
+        if (blockIdx.x == 0 && tid == 0 && ps.wait_ns) *ps.wait_ns = global_ns() - t0;
     }
     __syncthreads();
 
@@ -152,6 +225,21 @@ __global__ void __launch_bounds__(THREADS, MINB) tile_kernel(TileOp op, int64_t 
     // ragged tail: the last n % kGran elements, plain loads/stores
     if (blockIdx.x == 0 && tid < (int)(n - n4)) op.tail(n4 + tid);
     if constexpr (TileOp::kHasSum) grid_sum_to(op.acc(), sc, sum_out);
+    if constexpr (PEER) {
+        // completion rendezvous: the block that finishes last tells the peers and waits for theirs
+        __shared__ bool last_to_finish;
+        __syncthreads();                       // this block's tail stores are issued; thread 0's bulk stores are complete
+        if (tid == 0) {
+            __threadfence_system();            // ... and ordered before the count below for whoever observes it
+            last_to_finish = atomicAdd(ps.done, 1u) == gridDim.x - 1;
+        }
+        __syncthreads();
+        if (last_to_finish) {
+            if (tid == 0) *ps.done = 0u;       // ready for the next launch (stream order)
+            peer_publish(ps, ps.ch_out, ps.epoch_out);
+            peer_await(ps, ps.ch_out, ps.epoch_out);
+        }
+    }
 }
 
 // ---- the same pipeline over a device TABLE of tensors -------------------------------------------

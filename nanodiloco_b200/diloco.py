@@ -94,6 +94,7 @@ class Diloco:
         nvls_fraction: float = 0.75,
         grad_buffer: str = "auto",
         p2p_exchange: str = "auto",
+        p2p_fold=None,
     ):
         # diloco.py:17-20
         self.model = model
@@ -184,7 +185,7 @@ class Diloco:
         elif self.sync_mode == "p2p":
             from .sync import PeerContext
             self._peer = PeerContext(W, self.rank, n, elem_bytes=16 // gran, group=process_group,
-                                     device=dev, replicas=self.replicas, exchange=p2p_exchange)
+                                     device=dev, replicas=self.replicas, exchange=p2p_exchange, fold=p2p_fold)
             self._local = self._peer.local(wdtype)[:n]
         elif self.sync_mode == "nccl":
             if wdtype != torch.float32:

@@ -192,10 +192,11 @@ class PeerContext:
     """
 
     def __init__(self, world: int, rank: int, n_padded: int, *, elem_bytes: int = 4, group=None, device=None,
-                 replicas: int = 1, exchange: str = "auto"):
+                 replicas: int = 1, exchange: str = "auto", fold=None):
         """exchange: "pull" (the owner's kernel reads the remote copies), "push" (every worker writes its
         slices into the owners' staging slots first; needs (world/replicas)/world of the working copy's
-        size in extra peer memory per rank) or "auto" (ND_P2P_MODE if set, else pull)."""
+        size in extra peer memory per rank) or "auto" (ND_P2P_MODE if set, else pull).
+        fold: False brackets the pull kernel with two barrier launches instead of folding the rendezvous into it."""
         import os
         L = _lib.load()
         self.world, self.rank, self.group = world, rank, group
@@ -229,6 +230,8 @@ class PeerContext:
         self.replicas = int(replicas)
         if self.replicas != 1:
             _lib.check(L.nd_peer_set_replicas(self._h, self.replicas), "nd_peer_set_replicas")
+        if fold is not None:      # None: the library's default (one launch; ND_P2P_FOLD=0 for barrier launches)
+            _lib.check(L.nd_peer_set_fold(self._h, int(bool(fold))), "nd_peer_set_fold")
         if staging_bytes:
             _lib.check(L.nd_peer_set_staging(self._h, local_bytes, staging_bytes), "nd_peer_set_staging")
             _lib.check(L.nd_peer_set_mode(self._h, _lib.ND_PEER_PUSH), "nd_peer_set_mode")

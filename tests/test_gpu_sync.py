@@ -2,7 +2,9 @@
 wrapper, every way the worker copies can meet, against (a) the reference's golden fixtures and (b) the
 CPU oracle at sizes where every CTA runs many tiles and stages:
 
-  p2p          nd_outer_sync_p2p, pull: one fused kernel per GPU reading and writing NVLink peer memory
+  p2p          nd_outer_sync_p2p, pull: one fused kernel per GPU reading and writing NVLink peer memory, the two
+               rendezvous of the ranks folded into the kernel
+  p2p_nofold   the same with the rendezvous as barrier launches of their own
   p2p_push     nd_outer_sync_p2p, push: workers write their slices into the owners' staging, owners reduce locally
   p2p_bf16     bf16 working copy, fp32 master and momentum (extension, BASELINE config 2)
   p2p_offload  the 1/W master shard in pinned host memory (nd_outer_sync_p2p_offloaded)
@@ -28,8 +30,8 @@ import torch.multiprocessing as mp
 pytestmark = [pytest.mark.gpu, pytest.mark.timeout(1500)]
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
-MODES = ["p2p", "p2p_push", "p2p_bf16", "p2p_offload", "p2p_rep2", "nccl", "nvls", "hybrid"]
-GOLDEN_CASES = [("golden", m, b) for m, b in [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_push", 64.0),
+MODES = ["p2p", "p2p_nofold", "p2p_push", "p2p_bf16", "p2p_offload", "p2p_rep2", "nccl", "nvls", "hybrid"]
+GOLDEN_CASES = [("golden", m, b) for m, b in [("nccl", 0.002), ("nccl", 64.0), ("p2p", 64.0), ("p2p_nofold", 64.0), ("p2p_push", 64.0),
                                               ("p2p_offload", 64.0), ("p2p_bf16", 64.0), ("p2p_rep2", 64.0),
                                               ("nvls", 64.0), ("nvls", 0.002), ("hybrid", 0.002)]]
 # tiny Llama (57 tensors, 9,766,528 parameters: BASELINE configs[0]) and the 150M-class Llama (111 tensors,
@@ -73,6 +75,8 @@ def _diloco_kwargs(mode, bucket_mb, offload_chunk_mb=0.001):
         kw.update(p2p_exchange="push")
     elif sync == "p2p":
         kw.update(p2p_exchange="pull")
+    if mode == "p2p_nofold":
+        kw.update(p2p_fold=False)
     return kw
 
 
@@ -124,12 +128,12 @@ def _golden_case(mode, bucket_mb, world, rank):
             ok &= chk("np.allclose(master, z[f'params_r{r}'], rtol=1e-6, atol=1e-6 * np.abs(z", np.allclose(master, z[f"params_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"params_r{r}"]).max()))
             ok &= chk("np.allclose(mom, z[f'mom_r{r}'], rtol=1e-6, atol=1e-6 * np.abs(z[f'mom", np.allclose(mom, z[f"mom_r{r}"], rtol=1e-6, atol=1e-6 * np.abs(z[f"mom_r{r}"]).max()))
     ok &= chk("d.avg_sync_time > 0", d.avg_sync_time > 0)
-    if mode in ("p2p", "p2p_push"):
+    if mode in ("p2p", "p2p_nofold", "p2p_push"):
         w = d.avg_sync_wait_time
         ok &= chk("avg_sync_wait_time is a non-negative number", w is not None and w >= 0.0)
     c = d.sync_counters()
     ok &= chk("sync_counters: ms and NVLink GB/s of the last sync", c["ms"] > 0 and c["nvlink_gbs_per_dir"] > 0)
-    if mode in ("p2p", "p2p_push"):
+    if mode in ("p2p", "p2p_nofold", "p2p_push"):
         ok &= chk("sync_counters: wait + work = total", abs(c["wait_ms"] + c["work_ms"] - c["total_ms"]) < 1e-3)
     sd = d.state_dict()                       # collective: full master and momentum on every rank
     saved = torch.cat([v.reshape(-1) for v in d.layout.views(sd["master"])]).numpy()
@@ -299,7 +303,7 @@ def _large_case(mode, workload, world, rank):
         lo, hi = words.clone(), words.clone()
         dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
         ok &= chk("int(lo) == int(hi)", int(lo) == int(hi))
-        if mode in ("p2p", "p2p_push", "p2p_rep2"):            # the pseudo-gradient norm the kernel computes on the way
+        if mode in ("p2p", "p2p_nofold", "p2p_push", "p2p_rep2"):            # the pseudo-gradient norm the kernel computes on the way
             sq = torch.tensor([pg_sq], device=dev, dtype=torch.float64)
             dist.all_reduce(sq)
             got_norm, want_norm = float(d.last_outer_grad_norm), float(sq.sqrt())

@@ -55,6 +55,13 @@ PY
   ;;
 ref3)
   timeout 600 $TR --master-port 29572 bench.py --impl reference --gpus $N --steps 3 --warmup 1 2> $OUT/bench_n${N}_ref3_$TAG.err | grep '^{' > $OUT/bench_n${N}_ref3_$TAG.json; cut -c1-2000 $OUT/bench_n${N}_ref3_$TAG.json; tail -3 $OUT/bench_n${N}_ref3_$TAG.err;;
+fold)
+  run_bench fold 29581 $FAST --sync p2p --no-e2e
+  run_bench nofold 29582 $FAST --sync p2p --no-e2e --p2p-no-fold
+  run_bench fold_150m 29583 $FAST --sync p2p --no-e2e --workload llama150m
+  run_bench nofold_150m 29584 $FAST --sync p2p --no-e2e --workload llama150m --p2p-no-fold
+  run_bench fold_tiny 29585 $FAST --sync p2p --no-e2e --workload tiny
+  run_bench nofold_tiny 29586 $FAST --sync p2p --no-e2e --workload tiny --p2p-no-fold;;
 micro)
   timeout 600 $TR --master-port 29561 tools/microbench.py > $OUT/microbench_n${N}_$TAG.log 2>&1; tail -30 $OUT/microbench_n${N}_$TAG.log;;
 full)
