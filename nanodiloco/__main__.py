@@ -1,5 +1,8 @@
-"""`python -m nanodiloco` (reference nanodiloco/__main__.py:1-4)."""
-from nanodiloco_b200.main import main
+"""Entry point of `python -m nanodiloco` (the reference's nanodiloco/__main__.py:1-4): runs the drop-in
+training loop of nanodiloco_b200 with the reference's command-line flags."""
+import sys
+
+import nanodiloco_b200.main as _loop
 
 if __name__ == "__main__":
-    main()
+    sys.exit(_loop.main())
