@@ -623,6 +623,9 @@ def native_arm(args):
     from nanodiloco_b200.flat import FlatLayout
     from nanodiloco_b200.sync import SyncContext
 
+    # a benchmark's ranks reach every sync together: a rank that waits two minutes for a peer has lost it, and an
+    # error then beats spinning until the driver's own time limit (training jobs keep the library's 1800 s default)
+    os.environ.setdefault("ND_PEER_TIMEOUT_S", "120")
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback")
     world = int(os.environ.get("WORLD_SIZE", "1"))
