@@ -425,7 +425,9 @@ int nd_peer_set_mode(nd_peer_ctx* ctx, int mode);
  * working copies (the context of nd_outer_sync_p2p), `grads_ctx` the gradient buffers (a second
  * nd_peer_alloc / nd_peer_ctx_create with the same replicas setting); m and v point at element 0 of the full
  * flat moment buffers.  On return (stream order) the gradient buffer is zero and sumsq_total_out (nullable)
- * holds the squared norm of the averaged gradient.  An extension: the reference has no such mode. */
+ * holds the squared norm of the averaged gradient.  The first call on a gradient context allocates that
+ * context's norm scratch (a few KB, freed by nd_peer_ctx_destroy): make it outside any stream capture.
+ * An extension: the reference has no such mode. */
 int nd_inner_step_replicas(nd_peer_ctx* params_ctx, nd_peer_ctx* grads_ctx, float* m, float* v, int dtype,
                            int64_t n_padded, double lr, double beta1, double beta2, double eps,
                            double weight_decay, int64_t step, float max_norm, float* sumsq_total_out,
